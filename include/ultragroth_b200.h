@@ -1,0 +1,81 @@
+/* ultragroth_b200 -- internal CUDA C ABI.
+ *
+ * This is what a host prover calls INSTEAD of iden3/ffiasm: the reference's prover reaches its
+ * arithmetic engine through
+ *     E.g1/g2.multiMulByScalarMSM ...... src/groth16.cpp:55,58,61,64,154; src/ultra_groth.cpp:168,203-234,329
+ *     FFT<Fr>::fft / ifft / root ....... src/groth16.cpp:110-140;          src/ultra_groth.cpp:288-309
+ *     E.fr.mul/add/sub/fromMontgomery .. src/groth16.cpp:70-108,142-148;   build/fr.asm (Fr_raw*)
+ * and each entry point below names the call it replaces.  Plain C types only: pointers, sizes, an int
+ * status (0 = ok, nonzero = error, text via ugb_last_error()).  No exception crosses this boundary.
+ * Device pointers are raw CUDA device addresses (cudaMalloc / torch .data_ptr()); all work is enqueued
+ * on the context's own stream and every call that returns host data synchronises that stream.
+ * There is NO CPU fallback: without a B200 (sm_100) device ugb_ctx_create fails.
+ */
+#ifndef ULTRAGROTH_B200_H
+#define ULTRAGROTH_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ugb_ctx ugb_ctx;
+
+#define UGB_OK 0
+#define UGB_ERROR 1
+
+/* field selectors / vector op codes for ugb_field_vec_op */
+#define UGB_FIELD_FR 0
+#define UGB_FIELD_FQ 1
+#define UGB_OP_MUL 0        /* Fr_rawMMul        build/fr_raw_generic.cpp:107 */
+#define UGB_OP_ADD 1        /* Fr_rawAdd         build/fr_raw_generic.cpp:11  */
+#define UGB_OP_SUB 2        /* Fr_rawSub         build/fr_raw_generic.cpp:31  */
+#define UGB_OP_NEG 3        /* Fr_rawNeg         build/fr_raw_generic.cpp:68  */
+#define UGB_OP_TO_MONT 4    /* Fr_rawToMontgomery   build/fr_raw_generic.cpp:150 */
+#define UGB_OP_FROM_MONT 5  /* Fr_rawFromMontgomery build/fr_raw_generic.cpp:155 */
+#define UGB_OP_SQR 6        /* Fr_rawMSquare     build/fr_raw_generic.cpp:150 */
+
+const char* ugb_last_error(void);
+int ugb_device_count(void);
+
+int ugb_ctx_create(int device, ugb_ctx** out);
+void ugb_ctx_destroy(ugb_ctx* ctx);
+int ugb_sync(ugb_ctx* ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+uint64_t ugb_kernel_launches(ugb_ctx* ctx);
+/* raw cudaStream_t of the context, for CUDA-event timing on the launching stream */
+void* ugb_stream(ugb_ctx* ctx);
+
+int ugb_malloc(ugb_ctx* ctx, uint64_t bytes, void** dptr);
+int ugb_free(ugb_ctx* ctx, void* dptr);
+int ugb_memcpy_h2d(ugb_ctx* ctx, void* dst_dev, const void* src_host, uint64_t bytes);
+int ugb_memcpy_d2h(ugb_ctx* ctx, void* dst_host, const void* src_dev, uint64_t bytes);
+
+/* out[i] = a[i] (op) b[i] over n 32-byte elements, all device pointers (b ignored for unary ops).
+ * Replaces the E.fr.* loops of src/groth16.cpp:100-108 and is the parity kernel for build/fr.asm. */
+int ugb_field_vec_op(ugb_ctx* ctx, int field, int op, const void* d_a, const void* d_b, void* d_out, uint64_t n);
+
+/* result = sum_i scalar[index ? index[i] : i] * base[i], i < n.
+ * d_bases: n affine points in zkey layout (Montgomery; G1 64 B, G2 128 B; all-zero = infinity);
+ * d_scalars: raw 32-byte little-endian integers; d_index: optional u32 gather list (may be NULL);
+ * window_bits: 0 = choose automatically.  h_out: affine result in the same layout (host memory).
+ * Replaces E.g1/g2.multiMulByScalarMSM (src/groth16.cpp:55-64,154). */
+int ugb_msm_g1(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_index, uint64_t n,
+               int window_bits, void* h_out);
+int ugb_msm_g2(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_index, uint64_t n,
+               int window_bits, void* h_out);
+/* same, result left in extended-Jacobian XYZZ form (G1 128 B, G2 256 B): the partial sum one GPU
+ * contributes when the point range is sharded across GPUs */
+int ugb_msm_g1_xyzz(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_index, uint64_t n,
+                    int window_bits, void* h_out_xyzz);
+int ugb_msm_g2_xyzz(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_index, uint64_t n,
+                    int window_bits, void* h_out_xyzz);
+/* host-side reduction of `count` XYZZ partial sums (from several GPUs / ranks) to one affine point */
+int ugb_g1_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out_affine);
+int ugb_g2_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out_affine);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,57 @@
+"""ctypes binding of libultragroth_b200.so (the C ABI of include/ultragroth_b200.h and include/prover.h).
+
+The library is the product; this module only loads it.  It fails loudly when the shared object is
+missing -- there is no Python or CPU implementation to fall back to.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libultragroth_b200.so")
+
+_lib = None
+
+
+class UltraGrothError(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise UltraGrothError(
+                f"{LIB_PATH} is missing: build it with `python -m ultragroth_b200.build` "
+                "(nvcc, sm_100a). ultragroth_b200 has no CPU fallback.")
+        _lib = ctypes.CDLL(LIB_PATH)
+        _declare(_lib)
+    return _lib
+
+
+def _declare(L):
+    c = ctypes
+    vp, u64, i32 = c.c_void_p, c.c_uint64, c.c_int
+    L.ugb_last_error.restype = c.c_char_p
+    L.ugb_device_count.restype = i32
+    L.ugb_ctx_create.argtypes = [i32, c.POINTER(vp)]
+    L.ugb_ctx_destroy.argtypes = [vp]
+    L.ugb_ctx_destroy.restype = None
+    L.ugb_sync.argtypes = [vp]
+    L.ugb_kernel_launches.argtypes = [vp]
+    L.ugb_kernel_launches.restype = u64
+    L.ugb_stream.argtypes = [vp]
+    L.ugb_stream.restype = vp
+    L.ugb_malloc.argtypes = [vp, u64, c.POINTER(vp)]
+    L.ugb_free.argtypes = [vp, vp]
+    L.ugb_memcpy_h2d.argtypes = [vp, vp, vp, u64]
+    L.ugb_memcpy_d2h.argtypes = [vp, vp, vp, u64]
+    L.ugb_field_vec_op.argtypes = [vp, i32, i32, vp, vp, vp, u64]
+    for name in ("ugb_msm_g1", "ugb_msm_g2", "ugb_msm_g1_xyzz", "ugb_msm_g2_xyzz"):
+        getattr(L, name).argtypes = [vp, vp, vp, vp, u64, i32, vp]
+    L.ugb_g1_sum_xyzz_to_affine.argtypes = [vp, u64, vp]
+    L.ugb_g2_sum_xyzz_to_affine.argtypes = [vp, u64, vp]
+
+
+def check(rc):
+    if rc != 0:
+        raise UltraGrothError(lib().ugb_last_error().decode(errors="replace"))

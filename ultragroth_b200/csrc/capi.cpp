@@ -1,0 +1,137 @@
+// C ABI of include/ultragroth_b200.h: thin, exception-free wrappers over the C++ host layer.
+#include "../../include/ultragroth_b200.h"
+
+#include <cstring>
+#include <string>
+
+#include "device.hpp"
+#include "fieldops.hpp"
+#include "msm.hpp"
+
+using namespace ug;
+
+struct ugb_ctx {
+    DeviceCtx dev;
+    explicit ugb_ctx(int d) : dev(d) {}
+};
+
+static thread_local std::string g_last_error;
+
+#define UGB_TRY try {
+#define UGB_CATCH                                                     \
+    }                                                                 \
+    catch (const std::exception& e) { g_last_error = e.what(); return UGB_ERROR; } \
+    catch (...) { g_last_error = "unknown error"; return UGB_ERROR; } \
+    return UGB_OK;
+
+extern "C" {
+
+const char* ugb_last_error(void) { return g_last_error.c_str(); }
+
+int ugb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int ugb_ctx_create(int device, ugb_ctx** out) {
+    UGB_TRY
+    if (!out) throw std::invalid_argument("null ctx pointer");
+    *out = new ugb_ctx(device);
+    UGB_CATCH
+}
+void ugb_ctx_destroy(ugb_ctx* ctx) { delete ctx; }
+int ugb_sync(ugb_ctx* ctx) { UGB_TRY ctx->dev.sync(); UGB_CATCH }
+uint64_t ugb_kernel_launches(ugb_ctx* ctx) { return ctx->dev.kernel_launches; }
+void* ugb_stream(ugb_ctx* ctx) { return (void*)ctx->dev.stream; }
+
+int ugb_malloc(ugb_ctx* ctx, uint64_t bytes, void** dptr) {
+    UGB_TRY
+    ctx->dev.activate();
+    UG_CUDA_CHECK(cudaMalloc(dptr, bytes ? bytes : 16));
+    UGB_CATCH
+}
+int ugb_free(ugb_ctx* ctx, void* dptr) {
+    UGB_TRY
+    ctx->dev.activate();
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx->dev.stream));
+    UG_CUDA_CHECK(cudaFree(dptr));
+    UGB_CATCH
+}
+int ugb_memcpy_h2d(ugb_ctx* ctx, void* dst, const void* src, uint64_t bytes) {
+    UGB_TRY
+    ctx->dev.activate();
+    UG_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->dev.stream));
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx->dev.stream));
+    UGB_CATCH
+}
+int ugb_memcpy_d2h(ugb_ctx* ctx, void* dst, const void* src, uint64_t bytes) {
+    UGB_TRY
+    ctx->dev.activate();
+    UG_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->dev.stream));
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx->dev.stream));
+    UGB_CATCH
+}
+
+int ugb_field_vec_op(ugb_ctx* ctx, int field, int op, const void* d_a, const void* d_b, void* d_out, uint64_t n) {
+    UGB_TRY
+    field_vec_op(ctx->dev, field, op, d_a, d_b, d_out, n);
+    UGB_CATCH
+}
+
+int ugb_msm_g1_xyzz(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_index, uint64_t n,
+                    int window_bits, void* h_out) {
+    UGB_TRY
+    MsmDigits dg;
+    msm_sort_digits(ctx->dev, (const uint8_t*)d_scalars, d_index, n, window_bits, "capi", dg);
+    HG1XYZZ r;
+    msm_accumulate_g1(ctx->dev, d_bases, dg, &r);
+    memcpy(h_out, &r, sizeof(r));
+    UGB_CATCH
+}
+int ugb_msm_g2_xyzz(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_index, uint64_t n,
+                    int window_bits, void* h_out) {
+    UGB_TRY
+    MsmDigits dg;
+    msm_sort_digits(ctx->dev, (const uint8_t*)d_scalars, d_index, n, window_bits, "capi", dg);
+    HG2XYZZ r;
+    msm_accumulate_g2(ctx->dev, d_bases, dg, &r);
+    memcpy(h_out, &r, sizeof(r));
+    UGB_CATCH
+}
+int ugb_msm_g1(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_index, uint64_t n,
+               int window_bits, void* h_out) {
+    HG1XYZZ r;
+    int rc = ugb_msm_g1_xyzz(ctx, d_bases, d_scalars, d_index, n, window_bits, &r);
+    if (rc) return rc;
+    HG1Affine a = pt_to_affine(r);
+    memcpy(h_out, &a, sizeof(a));
+    return UGB_OK;
+}
+int ugb_msm_g2(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_index, uint64_t n,
+               int window_bits, void* h_out) {
+    HG2XYZZ r;
+    int rc = ugb_msm_g2_xyzz(ctx, d_bases, d_scalars, d_index, n, window_bits, &r);
+    if (rc) return rc;
+    HG2Affine a = pt_to_affine(r);
+    memcpy(h_out, &a, sizeof(a));
+    return UGB_OK;
+}
+int ugb_g1_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out) {
+    UGB_TRY
+    HG1XYZZ acc = HG1XYZZ::inf();
+    for (uint64_t i = 0; i < count; i++) { HG1XYZZ p; memcpy(&p, (const char*)h_partials + i * sizeof(p), sizeof(p)); pt_add(acc, p); }
+    HG1Affine a = pt_to_affine(acc);
+    memcpy(h_out, &a, sizeof(a));
+    UGB_CATCH
+}
+int ugb_g2_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out) {
+    UGB_TRY
+    HG2XYZZ acc = HG2XYZZ::inf();
+    for (uint64_t i = 0; i < count; i++) { HG2XYZZ p; memcpy(&p, (const char*)h_partials + i * sizeof(p), sizeof(p)); pt_add(acc, p); }
+    HG2Affine a = pt_to_affine(acc);
+    memcpy(h_out, &a, sizeof(a));
+    UGB_CATCH
+}
+
+}  // extern "C"

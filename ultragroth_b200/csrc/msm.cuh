@@ -1,0 +1,316 @@
+// Pippenger multi-scalar multiplication kernels for sm_100a (G1 and G2 via the field template F).
+//
+// Replaces ffiasm's Curve<F>::multiMulByScalarMSM (depends/ffiasm, absent), call sites
+// src/groth16.cpp:55,58,61,64,154 and src/ultra_groth.cpp:168,203,214,224,234,329:
+//   result = sum_i scalar_i * base_i,  bases affine Montgomery (all-zero = infinity),
+//   scalars raw (non-Montgomery) 32-byte little-endian integers.
+//
+// Pipeline (all on one stream, no host round trip until the final 256 partial sums):
+//   1. k_digits_count     signed c-bit digits of every scalar, histogram per (window, |digit|)
+//   2. scan               exclusive prefix sum of the histogram -> bucket start offsets
+//   3. k_digits_scatter   counting-sort scatter of (point index | sign) into bucket order
+//   4. k_accumulate       atomics-free segmented bucket accumulation: every thread owns an equal
+//                         slice of the SORTED entry list (so skewed scalar distributions cannot
+//                         unbalance it), adds affine points into an XYZZ accumulator and flushes at
+//                         bucket boundaries; runs cut by a slice boundary become (key, partial) pairs
+//   5. k_seg_reduce       segmented scan over those pairs (recursively, 128:2 per level)
+//   6. k_bucket_bits      U[p] = sum of buckets whose weight has bit p set (pure tree reductions)
+//   7. host               sum_p 2^p U[p] by Horner (255 doublings) -- O(1) serial work, as the
+//                         reference's own final double-and-add (north star: "reduced on the host")
+#pragma once
+#include "curve.cuh"
+#include "memops.cuh"
+
+namespace ug {
+
+// ---- scalar digits ----------------------------------------------------------------------------
+struct Scalar256 { uint32_t v[8]; };
+
+// reduce an arbitrary 256-bit scalar below r (s*P == (s mod r)*P on the r-torsion); at most 5 steps
+UG_HD void scalar_reduce(Scalar256& s) {
+    for (int it = 0; it < 6; it++) {
+        uint32_t t[8];
+        t[0] = sub_cc(s.v[0], FrParams::mod(0));
+#pragma unroll
+        for (int i = 1; i < 8; i++) t[i] = subc_cc(s.v[i], FrParams::mod(i));
+        uint32_t borrow = subc(0, 0);
+        if (borrow) break;
+#pragma unroll
+        for (int i = 0; i < 8; i++) s.v[i] = t[i];
+    }
+}
+
+UG_HD uint32_t scalar_bits(const Scalar256& s, int pos, int c) {
+    // bits [pos, pos+c) ; c <= 24 ; bits beyond 256 read as zero
+    int w = pos >> 5, off = pos & 31;
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        if (i == w) lo = s.v[i];
+        if (i == w + 1) hi = s.v[i];
+    }
+    uint64_t x = ((uint64_t)hi << 32) | lo;
+    return (uint32_t)(x >> off) & ((1u << c) - 1u);
+}
+
+// signed-digit recoding: digit in [-(B-1), B], B = 2^(c-1); emits (window, |d|-1, sign) via f
+template <class Fn>
+UG_HD void scalar_digits(const Scalar256& s, int c, int W, Fn f) {
+    uint32_t carry = 0;
+    const uint32_t B = 1u << (c - 1);
+    for (int w = 0; w < W; w++) {
+        uint32_t d = scalar_bits(s, w * c, c) + carry;
+        carry = 0;
+        bool neg = false;
+        if (d > B) { d = (1u << c) - d; neg = true; carry = 1; }
+        if (d != 0) f(w, d - 1, neg);
+    }
+}
+
+UG_D Scalar256 load_scalar(const uint8_t* scalars, const uint32_t* index, uint64_t i) {
+    uint64_t src = index ? (uint64_t)index[i] : i;
+    const uint4* p = reinterpret_cast<const uint4*>(scalars + src * 32);
+    uint4 a = __ldg(p), b = __ldg(p + 1);
+    Scalar256 s;
+    s.v[0] = a.x; s.v[1] = a.y; s.v[2] = a.z; s.v[3] = a.w;
+    s.v[4] = b.x; s.v[5] = b.y; s.v[6] = b.z; s.v[7] = b.w;
+    return s;
+}
+
+#if defined(__CUDACC__)
+
+__global__ void k_digits_count(const uint8_t* __restrict__ scalars, const uint32_t* __restrict__ index,
+                               uint64_t n, int c, int W, uint32_t* __restrict__ counts) {
+    const uint32_t B = 1u << (c - 1);
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        Scalar256 s = load_scalar(scalars, index, i);
+        scalar_reduce(s);
+        scalar_digits(s, c, W, [&](int w, uint32_t b, bool) { atomicAdd(&counts[(uint32_t)w * B + b], 1u); });
+    }
+}
+
+__global__ void k_digits_scatter(const uint8_t* __restrict__ scalars, const uint32_t* __restrict__ index,
+                                 uint64_t n, int c, int W, uint32_t* __restrict__ cursor,
+                                 uint32_t* __restrict__ entries) {
+    const uint32_t B = 1u << (c - 1);
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        Scalar256 s = load_scalar(scalars, index, i);
+        scalar_reduce(s);
+        scalar_digits(s, c, W, [&](int w, uint32_t b, bool neg) {
+            uint32_t pos = atomicAdd(&cursor[(uint32_t)w * B + b], 1u);
+            entries[pos] = (uint32_t)i | (neg ? 0x80000000u : 0u);
+        });
+    }
+}
+
+// ---- exclusive scan of the histogram (3 small launches; tile = 2048 counters) -----------------
+constexpr int SCAN_BS = 256;
+constexpr int SCAN_TILE = 2048;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_t* total) {
+    __shared__ uint32_t warp_sums[8];
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_sums[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t s = lane < 8 ? warp_sums[lane] : 0;
+#pragma unroll
+        for (int d = 1; d < 8; d <<= 1) {
+            uint32_t y = __shfl_up_sync(0xffffffffu, s, d);
+            if (lane >= d) s += y;
+        }
+        if (lane < 8) warp_sums[lane] = s;
+    }
+    __syncthreads();
+    uint32_t base = wid ? warp_sums[wid - 1] : 0;
+    if (total) *total = warp_sums[7];
+    uint32_t r = base + x - v;
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(SCAN_BS) k_scan_tile_sums(const uint32_t* __restrict__ in, uint32_t n, uint32_t* __restrict__ tile_sums) {
+    uint32_t base = blockIdx.x * SCAN_TILE;
+    uint32_t s = 0;
+    for (int k = 0; k < SCAN_TILE / SCAN_BS; k++) {
+        uint32_t i = base + k * SCAN_BS + threadIdx.x;
+        if (i < n) s += in[i];
+    }
+    uint32_t tot;
+    block_exclusive_scan_256(s, &tot);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+}
+
+// single block: exclusive scan of up to 256*per tile sums, also writes the grand total to out_total
+__global__ void __launch_bounds__(SCAN_BS) k_scan_tiles(uint32_t* tile_sums, uint32_t ntiles, uint32_t* out_total) {
+    uint32_t per = (ntiles + SCAN_BS - 1) / SCAN_BS;
+    uint32_t lo = threadIdx.x * per, hi = min(lo + per, ntiles);
+    uint32_t s = 0;
+    for (uint32_t i = lo; i < hi; i++) s += tile_sums[i];
+    uint32_t tot;
+    uint32_t ex = block_exclusive_scan_256(s, &tot);
+    for (uint32_t i = lo; i < hi; i++) { uint32_t v = tile_sums[i]; tile_sums[i] = ex; ex += v; }
+    if (threadIdx.x == 0) *out_total = tot;
+}
+
+__global__ void __launch_bounds__(SCAN_BS) k_scan_apply(const uint32_t* __restrict__ in, uint32_t n, const uint32_t* __restrict__ tile_offs,
+                                                       uint32_t* __restrict__ out) {
+    // thread t owns 8 consecutive counters of the tile
+    uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * 8;
+    uint32_t v[8];
+    uint32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { v[k] = (base + k < n) ? in[base + k] : 0; s += v[k]; }
+    uint32_t ex = block_exclusive_scan_256(s, nullptr) + tile_offs[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { if (base + k < n) out[base + k] = ex; ex += v[k]; }
+}
+
+// ---- bucket accumulation ----------------------------------------------------------------------
+// starts[0..NB] = bucket offsets into entries (starts[NB] = total M).  Thread t owns entries
+// [t*L, (t+1)*L), L = ceil(M/T).  Outputs: buckets[key] for runs strictly inside the slice,
+// (pkeys, ppts)[2t], [2t+1] for the first and last run of the slice.
+template <class F>
+__global__ void __launch_bounds__(128) k_accumulate(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
+                                                    const uint32_t* __restrict__ starts, uint32_t NB,
+                                                    XYZZ<F>* __restrict__ buckets, uint32_t* __restrict__ pkeys,
+                                                    XYZZ<F>* __restrict__ ppts) {
+    const uint32_t T = gridDim.x * blockDim.x;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t M = starts[NB];
+    const uint32_t L = (uint32_t)(((uint64_t)M + T - 1) / T);
+    const uint64_t lo64 = (uint64_t)t * L;
+    if (L == 0 || lo64 >= M) {
+        pkeys[2 * t] = NB; pkeys[2 * t + 1] = NB;
+        st_g(&ppts[2 * t], XYZZ<F>::inf());
+        st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
+        return;
+    }
+    const uint32_t lo = (uint32_t)lo64;
+    const uint32_t hi = (uint32_t)min((uint64_t)M, lo64 + L);
+    // smallest key with starts[key+1] > lo
+    uint32_t a = 0, b = NB - 1;
+    while (a < b) {
+        uint32_t mid = (a + b) >> 1;
+        if (starts[mid + 1] > lo) b = mid; else a = mid + 1;
+    }
+    uint32_t key = a;
+    uint32_t end = starts[key + 1];
+    XYZZ<F> acc = XYZZ<F>::inf();
+    bool first = true;
+    uint32_t e = entries[lo];
+    Affine<F> pt = ld_nc(&bases[e & 0x7fffffffu]);
+    for (uint32_t pos = lo; pos < hi; pos++) {
+        if (pos == end) {
+            if (first) { pkeys[2 * t] = key; st_g(&ppts[2 * t], acc); first = false; }
+            else st_g(&buckets[key], acc);
+            acc = XYZZ<F>::inf();
+            do { key++; end = starts[key + 1]; } while (end <= pos);
+        }
+        // prefetch the next point while this one is being added
+        uint32_t e_next = 0;
+        Affine<F> pt_next;
+        bool has_next = pos + 1 < hi;
+        if (has_next) { e_next = entries[pos + 1]; pt_next = ld_nc(&bases[e_next & 0x7fffffffu]); }
+        pt_madd(acc, pt, (e >> 31) != 0);
+        if (has_next) { e = e_next; pt = pt_next; }
+    }
+    if (first) {
+        pkeys[2 * t] = key; st_g(&ppts[2 * t], acc);
+        pkeys[2 * t + 1] = key; st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
+    } else {
+        pkeys[2 * t + 1] = key; st_g(&ppts[2 * t + 1], acc);
+    }
+}
+
+// ---- segmented reduction of (key, point) pairs sorted by key -----------------------------------
+constexpr int SEG_BS = 128;
+
+template <class F>
+__global__ void __launch_bounds__(SEG_BS) k_seg_reduce(const uint32_t* __restrict__ keys, const XYZZ<F>* __restrict__ pts, uint32_t K,
+                                                       uint32_t NB, XYZZ<F>* __restrict__ buckets,
+                                                       uint32_t* __restrict__ out_keys, XYZZ<F>* __restrict__ out_pts, int final_pass) {
+    __shared__ XYZZ<F> sh[SEG_BS];
+    __shared__ uint32_t shk[SEG_BS];
+    const int tid = threadIdx.x;
+    const uint32_t i = blockIdx.x * SEG_BS + tid;
+    uint32_t key = NB;
+    XYZZ<F> val = XYZZ<F>::inf();
+    if (i < K) { key = keys[i]; val = ld_g(&pts[i]); }
+    shk[tid] = key;
+    for (int d = 1; d < SEG_BS; d <<= 1) {
+        sh[tid] = val;
+        __syncthreads();
+        if (tid >= d && shk[tid - d] == key) {
+            XYZZ<F> other = sh[tid - d];
+            pt_add(val, other);
+        }
+        __syncthreads();
+    }
+    const bool is_last = (tid == SEG_BS - 1) || (shk[tid + 1] != key);
+    if (!is_last) return;
+    const bool touches_start = (shk[0] == key);
+    const bool touches_end = (tid == SEG_BS - 1);
+    if (final_pass || !(touches_start || touches_end)) {
+        if (key < NB) st_g(&buckets[key], val);
+        return;
+    }
+    const uint32_t s0 = 2 * blockIdx.x, s1 = s0 + 1;
+    if (touches_start) {
+        out_keys[s0] = key; st_g(&out_pts[s0], val);
+        if (touches_end) { out_keys[s1] = key; st_g(&out_pts[s1], XYZZ<F>::inf()); }
+    } else {  // touches_end only
+        out_keys[s1] = key; st_g(&out_pts[s1], val);
+    }
+}
+
+// ---- bucket reduction: U[w*c + k] = sum over buckets j of window w whose weight (j+1) has bit k set
+constexpr int BITS_BS = 128;
+
+template <class F>
+__global__ void __launch_bounds__(BITS_BS) k_bucket_bits(const XYZZ<F>* __restrict__ buckets, int c, int S,
+                                                         XYZZ<F>* __restrict__ out /* [W][c][S] */) {
+    __shared__ XYZZ<F> sh[BITS_BS];
+    const int s = blockIdx.x, k = blockIdx.y, w = blockIdx.z;
+    const uint32_t B = 1u << (c - 1);
+    const XYZZ<F>* wb = buckets + (size_t)w * B;
+    XYZZ<F> acc = XYZZ<F>::inf();
+    if (k == c - 1) {
+        if (s == 0 && threadIdx.x == 0) acc = ld_g(&wb[B - 1]);
+    } else {
+        const uint32_t half = B >> 1;               // number of weights < B with bit k set
+        const uint32_t per = (half + S - 1) / S;
+        const uint32_t m_lo = s * per, m_hi = min(half, m_lo + per);
+        for (uint32_t m = m_lo + threadIdx.x; m < m_hi; m += BITS_BS) {
+            uint32_t v = ((m >> k) << (k + 1)) | (1u << k) | (m & ((1u << k) - 1u));
+            XYZZ<F> p = ld_g(&wb[v - 1]);
+            pt_add(acc, p);
+        }
+    }
+    for (int d = BITS_BS / 2; d > 0; d >>= 1) {
+        sh[threadIdx.x] = acc;
+        __syncthreads();
+        if (threadIdx.x < d) { XYZZ<F> o = sh[threadIdx.x + d]; pt_add(acc, o); }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) st_g(&out[((size_t)w * c + k) * S + s], acc);
+}
+
+template <class F>
+__global__ void k_sum_slices(const XYZZ<F>* __restrict__ in, int S, int count, XYZZ<F>* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    XYZZ<F> acc = ld_g(&in[(size_t)i * S]);
+    for (int s = 1; s < S; s++) { XYZZ<F> p = ld_g(&in[(size_t)i * S + s]); pt_add(acc, p); }
+    st_g(&out[i], acc);
+}
+
+#endif  // __CUDACC__
+
+}  // namespace ug

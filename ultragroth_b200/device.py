@@ -1,0 +1,94 @@
+"""Thin object wrapper over the internal CUDA C ABI (include/ultragroth_b200.h)."""
+import ctypes
+
+import numpy as np
+
+from ._lib import check, lib
+
+FIELD_FR, FIELD_FQ = 0, 1
+OP_MUL, OP_ADD, OP_SUB, OP_NEG, OP_TO_MONT, OP_FROM_MONT, OP_SQR = range(7)
+
+
+class DeviceArray:
+    def __init__(self, ctx, nbytes):
+        self.ctx = ctx
+        self.nbytes = int(nbytes)
+        p = ctypes.c_void_p()
+        check(lib().ugb_malloc(ctx.handle, self.nbytes, ctypes.byref(p)))
+        self.ptr = p.value
+
+    def free(self):
+        if self.ptr:
+            lib().ugb_free(self.ctx.handle, self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Context:
+    """One CUDA device + stream + workspace (ugb_ctx)."""
+
+    def __init__(self, device=0):
+        h = ctypes.c_void_p()
+        check(lib().ugb_ctx_create(int(device), ctypes.byref(h)))
+        self.handle = h
+        self.device = device
+
+    def close(self):
+        if self.handle:
+            lib().ugb_ctx_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # memory ------------------------------------------------------------------------------
+    def upload(self, data) -> DeviceArray:
+        buf = np.ascontiguousarray(np.frombuffer(data, dtype=np.uint8)) if isinstance(data, (bytes, bytearray, memoryview)) \
+            else np.ascontiguousarray(data)
+        arr = DeviceArray(self, max(buf.nbytes, 16))
+        if buf.nbytes:
+            check(lib().ugb_memcpy_h2d(self.handle, arr.ptr, buf.ctypes.data, buf.nbytes))
+        arr.nbytes = buf.nbytes
+        return arr
+
+    def empty(self, nbytes) -> DeviceArray:
+        return DeviceArray(self, nbytes)
+
+    def download(self, arr: DeviceArray, nbytes=None) -> bytes:
+        n = arr.nbytes if nbytes is None else nbytes
+        out = np.empty(n, dtype=np.uint8)
+        if n:
+            check(lib().ugb_memcpy_d2h(self.handle, out.ctypes.data, arr.ptr, n))
+        return out.tobytes()
+
+    def sync(self):
+        check(lib().ugb_sync(self.handle))
+
+    @property
+    def kernel_launches(self):
+        return int(lib().ugb_kernel_launches(self.handle))
+
+    @property
+    def stream(self):
+        return lib().ugb_stream(self.handle)
+
+    # ops ---------------------------------------------------------------------------------
+    def field_vec_op(self, field, op, a: DeviceArray, b: DeviceArray, out: DeviceArray, n):
+        check(lib().ugb_field_vec_op(self.handle, field, op, a.ptr, b.ptr if b is not None else None, out.ptr, n))
+
+    def msm(self, group, bases: DeviceArray, scalars: DeviceArray, n, index: DeviceArray = None, window_bits=0,
+            xyzz=False, scalar_offset=0) -> bytes:
+        size = (64 if group == 1 else 128) * (2 if xyzz else 1)
+        out = ctypes.create_string_buffer(size)
+        fn = getattr(lib(), f"ugb_msm_g{group}" + ("_xyzz" if xyzz else ""))
+        check(fn(self.handle, bases.ptr, scalars.ptr + 32 * scalar_offset, index.ptr if index is not None else None,
+                 n, window_bits, out))
+        return out.raw
