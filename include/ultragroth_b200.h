@@ -75,6 +75,34 @@ int ugb_msm_g2_xyzz(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, co
 int ugb_g1_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out_affine);
 int ugb_g2_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out_affine);
 
+/* In-place Fr transform of 2^logn Montgomery-form elements on the device, natural order in and out;
+ * inverse != 0 includes the 1/n scale.  Replaces FFT<Fr>::fft / ifft (src/groth16.cpp:112,122,132 and
+ * :120,130,140; src/ultra_groth.cpp:289-309). */
+int ugb_ntt(ugb_ctx* ctx, void* d_data, int logn, int inverse);
+/* The fused H-pipeline transform of src/groth16.cpp:110-140 on `count` (1..3) vectors:
+ * ifft, multiply by omega_2n^i, fft -- evaluations on the odd coset, natural order in and out. */
+int ugb_coset_transform(ugb_ctx* ctx, void* const* d_vecs, int count, int logn);
+
+/* ---- extensions on the reference's prover objects (void* from *_prover_create, include/prover.h) ----
+ * The reference draws r, s (and UltraGroth's r_k) from randombytes_buf (src/groth16.cpp:165-166,
+ * src/ultra_groth.cpp:173,345-346) and has no way to pin them; parity tests need one.  r32/s32/rk32 are
+ * 32-byte little-endian raw integers (< 2^248 to stay inside the reference's range); NULL r32 or s32
+ * returns the prover to random blinding. */
+int ugb_prover_set_blinding(void* prover_object, const void* r32, const void* s32, const void* rk32);
+/* the H-MSM scalars (canonical 32-byte integers, domainSize of them) of the last proof */
+int ugb_prover_last_h(void* prover_object, void* h_out, uint64_t bytes);
+/* per-stage CUDA-event times (ms) of the last proof: upload, round, lookup, sort_w, msm_a, msm_b1, msm_b2,
+ * msm_c, spmv, intt, ntt, hfinal, sort_h, msm_h, total */
+int ugb_prover_set_timing(void* prover_object, int enable);
+int ugb_prover_last_times(void* prover_object, float* out, int count);
+uint64_t ugb_prover_kernel_launches(void* prover_object);
+void* ugb_prover_stream(void* prover_object);
+
+/* ---- microbenchmarks for the roofline denominators ----
+ * kind 0: independent 32-bit IMAD chains; 1: IMAD.WIDE (mad.wide.u32) chains; 2: dependent Fq Montgomery
+ * products (4 chains per thread).  Returns operations per second in *ops_per_s. */
+int ugb_bench_int_pipe(ugb_ctx* ctx, int kind, double* ops_per_s);
+
 #ifdef __cplusplus
 }
 #endif

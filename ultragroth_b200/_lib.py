@@ -50,6 +50,33 @@ def _declare(L):
         getattr(L, name).argtypes = [vp, vp, vp, vp, u64, i32, vp]
     L.ugb_g1_sum_xyzz_to_affine.argtypes = [vp, u64, vp]
     L.ugb_g2_sum_xyzz_to_affine.argtypes = [vp, u64, vp]
+    L.ugb_ntt.argtypes = [vp, vp, i32, i32]
+    L.ugb_coset_transform.argtypes = [vp, c.POINTER(vp), i32, i32]
+    L.ugb_bench_int_pipe.argtypes = [vp, i32, c.POINTER(c.c_double)]
+    # prover extensions
+    L.ugb_prover_set_blinding.argtypes = [vp, vp, vp, vp]
+    L.ugb_prover_last_h.argtypes = [vp, vp, u64]
+    L.ugb_prover_set_timing.argtypes = [vp, i32]
+    L.ugb_prover_last_times.argtypes = [vp, c.POINTER(c.c_float), i32]
+    L.ugb_prover_kernel_launches.argtypes = [vp]
+    L.ugb_prover_kernel_launches.restype = u64
+    L.ugb_prover_stream.argtypes = [vp]
+    L.ugb_prover_stream.restype = vp
+    # the reference's prover C API (include/prover.h)
+    ull, cp = c.c_ulonglong, c.c_char_p
+    pull = c.POINTER(ull)
+    for pre in ("groth16", "ultra_groth"):
+        getattr(L, pre + "_public_size_for_zkey_buf").argtypes = [vp, ull, pull, vp, ull]
+        getattr(L, pre + "_public_size_for_zkey_file").argtypes = [cp, pull, vp, ull]
+        getattr(L, pre + "_proof_size").argtypes = [pull]
+        getattr(L, pre + "_proof_size").restype = None
+        getattr(L, pre + "_prover_create").argtypes = [c.POINTER(vp), vp, ull, vp, ull]
+        getattr(L, pre + "_prover_create_zkey_file").argtypes = [c.POINTER(vp), cp, vp, ull]
+        getattr(L, pre + "_prover_prove").argtypes = [vp, vp, ull, vp, pull, vp, pull, vp, ull]
+        getattr(L, pre + "_prover_destroy").argtypes = [vp]
+        getattr(L, pre + "_prover_destroy").restype = None
+        getattr(L, pre + "_prover").argtypes = [vp, ull, vp, ull, vp, pull, vp, pull, vp, ull]
+        getattr(L, pre + "_prover_zkey_file").argtypes = [cp, vp, ull, vp, pull, vp, pull, vp, ull]
 
 
 def check(rc):

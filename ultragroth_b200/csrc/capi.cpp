@@ -7,12 +7,16 @@
 #include "device.hpp"
 #include "fieldops.hpp"
 #include "msm.hpp"
+#include "ntt.hpp"
+
+namespace ug { double bench_int_pipe(DeviceCtx& ctx, int kind); }
 
 using namespace ug;
 
 struct ugb_ctx {
     DeviceCtx dev;
-    explicit ugb_ctx(int d) : dev(d) {}
+    NttTables tabs;
+    explicit ugb_ctx(int d) : dev(d), tabs(dev) {}
 };
 
 static thread_local std::string g_last_error;
@@ -131,6 +135,26 @@ int ugb_g2_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_ou
     for (uint64_t i = 0; i < count; i++) { HG2XYZZ p; memcpy(&p, (const char*)h_partials + i * sizeof(p), sizeof(p)); pt_add(acc, p); }
     HG2Affine a = pt_to_affine(acc);
     memcpy(h_out, &a, sizeof(a));
+    UGB_CATCH
+}
+
+int ugb_ntt(ugb_ctx* ctx, void* d_data, int logn, int inverse) {
+    UGB_TRY
+    ntt_natural(ctx->dev, ctx->tabs, (Fr*)d_data, logn, inverse != 0);
+    UGB_CATCH
+}
+int ugb_coset_transform(ugb_ctx* ctx, void* const* d_vecs, int count, int logn) {
+    UGB_TRY
+    if (count < 1 || count > 3) throw std::invalid_argument("count must be 1..3");
+    Fr* v[3] = {nullptr, nullptr, nullptr};
+    for (int i = 0; i < count; i++) v[i] = (Fr*)d_vecs[i];
+    ntt_run(ctx->dev, ctx->tabs, v, count, logn, NTT_NATURAL_TO_BITREV, true, ctx->tabs.coset_inv_bitrev(logn), nullptr);
+    ntt_run(ctx->dev, ctx->tabs, v, count, logn, NTT_BITREV_TO_NATURAL, false, nullptr, nullptr);
+    UGB_CATCH
+}
+int ugb_bench_int_pipe(ugb_ctx* ctx, int kind, double* ops_per_s) {
+    UGB_TRY
+    *ops_per_s = bench_int_pipe(ctx->dev, kind);
     UGB_CATCH
 }
 

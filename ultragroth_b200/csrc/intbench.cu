@@ -1,0 +1,85 @@
+// Integer-pipe microbenchmarks: the roofline denominators for the MSM / NTT kernels (SURVEY.md 8(d):
+// "imad_peak must be microbenchmarked on the box").  Every thread runs 8 independent chains so the
+// 4-cycle IMAD latency is covered without relying on occupancy.
+#include "curve.cuh"
+#include "device.hpp"
+
+namespace ug {
+
+constexpr int IB_ITERS = 4096;
+
+__global__ void __launch_bounds__(256) k_bench_imad(uint32_t* out, uint32_t seed) {
+    uint32_t a[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = seed + threadIdx.x * 8 + i;
+    uint32_t m = seed | 1u;
+    for (int it = 0; it < IB_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(m), "r"(a[(i + 1) & 7]));
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s ^= a[i];
+    if (s == 0x12345678u) out[0] = s;
+}
+
+__global__ void __launch_bounds__(256) k_bench_imad_wide(uint64_t* out, uint32_t seed) {
+    uint64_t a[8];
+    uint32_t x[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { a[i] = seed + threadIdx.x * 8 + i; x[i] = seed * (i + 3) + threadIdx.x; }
+    uint32_t m = seed | 1u;
+    for (int it = 0; it < IB_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(a[i]) : "r"(x[i]), "r"(m));
+    }
+    uint64_t s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s ^= a[i];
+    if (s == 0x12345678u) out[0] = s;
+}
+
+constexpr int MB_ITERS = 256;
+__global__ void __launch_bounds__(256) k_bench_modmul(Fq* out, uint32_t seed) {
+    Fq a[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        a[i] = Fq::one();
+        a[i].v[0] += seed + threadIdx.x + i;
+    }
+    Fq m = Fq::rsquared();
+    for (int it = 0; it < MB_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) a[i] = fp_mul(a[i], m);
+    }
+    Fq s = fp_add(fp_add(a[0], a[1]), fp_add(a[2], a[3]));
+    if (s.v[0] == 0x12345678u && s.v[7] == 1) out[0] = s;
+}
+
+double bench_int_pipe(DeviceCtx& ctx, int kind) {
+    ctx.activate();
+    void* d = ctx.workspace("intbench", 256);
+    cudaEvent_t e0, e1;
+    UG_CUDA_CHECK(cudaEventCreate(&e0));
+    UG_CUDA_CHECK(cudaEventCreate(&e1));
+    const int blocks = ctx.sm_count * 8;
+    double ops = 0;
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {
+        UG_CUDA_CHECK(cudaEventRecord(e0, ctx.stream));
+        if (kind == 0) { k_bench_imad<<<blocks, 256, 0, ctx.stream>>>((uint32_t*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
+        else if (kind == 1) { k_bench_imad_wide<<<blocks, 256, 0, ctx.stream>>>((uint64_t*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
+        else { k_bench_modmul<<<blocks, 256, 0, ctx.stream>>>((Fq*)d, 7 + rep); ops = (double)blocks * 256 * 4 * MB_ITERS; }
+        UG_LAUNCH_CHECK(ctx);
+        UG_CUDA_CHECK(cudaEventRecord(e1, ctx.stream));
+        UG_CUDA_CHECK(cudaEventSynchronize(e1));
+        float ms;
+        UG_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0) best = std::min(best, ms);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return ops / (best * 1e-3);
+}
+
+}  // namespace ug

@@ -1,0 +1,533 @@
+// The reference's prover C API (include/prover.h == src/prover.h) on top of the device prover.
+//
+// Mirrors src/prover.cpp: the same wrapper objects (Groth16Prover :144-216, UltraGrothProver :219-309),
+// validation order, error codes and messages, buffer-size rules and strncpy output convention.  The O(1)
+// tail of a proof -- blinding, proof assembly, affine conversion, JSON (src/groth16.cpp:158-250,
+// src/ultra_groth.cpp:161-184,337-399,476-513) -- runs on the host, as it does in the reference.
+#include "../../include/prover.h"
+#include "../../include/ultragroth_b200.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <memory>
+#include <random>
+#include <string>
+
+#include "hostio.hpp"
+#include "prover_dev.hpp"
+
+using namespace ug;
+
+namespace {
+
+class ShortBufferException : public std::invalid_argument {
+public:
+    explicit ShortBufferException(const std::string& msg) : std::invalid_argument(msg) {}
+};
+class InvalidWitnessLengthException : public std::invalid_argument {
+public:
+    explicit InvalidWitnessLengthException(const std::string& msg) : std::invalid_argument(msg) {}
+};
+
+void CopyError(char* error_msg, unsigned long long maxsize, const char* str) {
+    if (error_msg) strncpy(error_msg, str, maxsize);
+}
+
+unsigned long long ProofBufferMinSize() { return 810; }
+unsigned long long ProofBufferMinSizeUltraGroth() { return 1400; }
+unsigned long long PublicBufferMinSize(unsigned long long count) { return count * 82 + 4; }
+
+void CheckAndUpdateBufferSizes(unsigned long long proofCalcSize, unsigned long long* proofSize, unsigned long long publicCalcSize,
+                               unsigned long long* publicSize, const std::string& type) {
+    if (*proofSize < proofCalcSize)
+        throw ShortBufferException("Proof buffer is too short. " + type + " size: " + std::to_string(proofCalcSize) +
+                                   ", actual size: " + std::to_string(*proofSize));
+    if (*publicSize < publicCalcSize)
+        throw ShortBufferException("Public buffer is too short. " + type + " size: " + std::to_string(publicCalcSize) +
+                                   ", actual size: " + std::to_string(*publicSize));
+}
+
+// ---- host curve helpers (O(1) work per proof) ----------------------------------------------------
+struct Scalar { uint64_t v[4]; };
+
+template <class HF>
+XYZZ<HF> pt_mul(const XYZZ<HF>& p, const Scalar& k) {  // E.g1.mulByScalar: plain double-and-add
+    XYZZ<HF> acc = XYZZ<HF>::inf();
+    for (int i = 255; i >= 0; i--) {
+        acc = pt_dbl(acc);
+        if ((k.v[i >> 6] >> (i & 63)) & 1) pt_add(acc, p);
+    }
+    return acc;
+}
+template <class HF>
+XYZZ<HF> from_affine_bytes(const uint8_t* p) {
+    Affine<HF> a;
+    memcpy(&a, p, sizeof(a));
+    return XYZZ<HF>::from_affine(a);
+}
+
+bool scalar_geq_r(const Scalar& s) {
+    for (int i = 3; i >= 0; i--) {
+        if (s.v[i] > HFrParams::mod[i]) return true;
+        if (s.v[i] < HFrParams::mod[i]) return false;
+    }
+    return true;
+}
+Scalar scalar_mod_r(Scalar s) {
+    while (scalar_geq_r(s)) {
+        unsigned __int128 borrow = 0;
+        for (int i = 0; i < 4; i++) {
+            unsigned __int128 d = (unsigned __int128)s.v[i] - HFrParams::mod[i] - (uint64_t)borrow;
+            s.v[i] = (uint64_t)d;
+            borrow = (d >> 64) & 1;
+        }
+    }
+    return s;
+}
+// E.fr.mul(rs, r, s); E.fr.toMontgomery(rs, rs)  (src/groth16.cpp:191-192)  ==  r*s mod r as a raw integer
+Scalar scalar_mul_mod_r(const Scalar& a, const Scalar& b) {
+    HFr x, y;
+    memcpy(&x, &a, 32);
+    memcpy(&y, &b, 32);
+    HFr m = fmul(x, y);   // a*b*R^-1
+    HFr t = to_mont(m);   // a*b
+    Scalar out;
+    memcpy(&out, &t, 32);
+    return out;
+}
+
+// randombytes_buf(&r.v[0], sizeof(r) - 1): 31 random bytes, top byte zero (src/groth16.cpp:165-166)
+Scalar random_blinding() {
+    Scalar s;
+    memset(&s, 0, sizeof(s));
+    FILE* f = fopen("/dev/urandom", "rb");
+    bool ok = false;
+    if (f) {
+        ok = fread(&s, 1, 31, f) == 31;
+        fclose(f);
+    }
+    if (!ok) {
+        std::random_device rd;
+        uint8_t* p = (uint8_t*)&s;
+        for (int i = 0; i < 31; i++) p[i] = (uint8_t)rd();
+    }
+    return s;
+}
+
+std::string g1_json(const HG1Affine& p) { return "[\"" + to_dec(p.x) + "\",\"" + to_dec(p.y) + "\",\"1\"]"; }
+std::string g2_json(const HG2Affine& p) {
+    return "[[\"" + to_dec(p.x.a) + "\",\"" + to_dec(p.x.b) + "\"],[\"" + to_dec(p.y.a) + "\",\"" + to_dec(p.y.b) + "\"],[\"1\",\"0\"]]";
+}
+
+// BuildPublicString (src/prover.cpp:89-117): nlohmann dump() of an array of decimal strings ("null" when empty)
+std::string public_json(const uint8_t* signals /* from index 1 */, uint32_t nPublic, uint32_t skip_index) {
+    std::string out;
+    bool any = false;
+    for (uint32_t i = 1; i <= nPublic; i++) {
+        if (i == skip_index) continue;
+        Scalar s;
+        memcpy(&s, signals + (size_t)(i - 1) * 32, 32);
+        s = scalar_mod_r(s);
+        out += any ? ",\"" : "[\"";
+        out += u256_to_dec(s.v);
+        out += "\"";
+        any = true;
+    }
+    return any ? out + "]" : "null";
+}
+
+struct Blinding {
+    bool fixed = false;
+    Scalar r, s, rk;
+};
+
+// src/groth16.cpp:168-200 and src/ultra_groth.cpp:353-396
+void assemble(const ZkeyHeader& h, const ProofMsms& m, const Scalar& r, const Scalar& s, const Scalar* rk, HG1Affine& A, HG2Affine& B,
+              HG1Affine& C) {
+    HG1XYZZ alpha1 = from_affine_bytes<HFq>(h.alpha1), beta1 = from_affine_bytes<HFq>(h.beta1), delta1 = from_affine_bytes<HFq>(h.final_delta1);
+    HG2XYZZ beta2 = from_affine_bytes<HFq2>(h.beta2), delta2 = from_affine_bytes<HFq2>(h.final_delta2);
+    HG1XYZZ pi_a = m.a, pib1 = m.b1, pi_c = m.c;
+    HG2XYZZ pi_b = m.b2;
+    pt_add(pi_a, alpha1);
+    pt_add(pi_a, pt_mul(delta1, r));
+    pt_add(pi_b, beta2);
+    pt_add(pi_b, pt_mul(delta2, s));
+    pt_add(pib1, beta1);
+    pt_add(pib1, pt_mul(delta1, s));
+    pt_add(pi_c, m.h);
+    pt_add(pi_c, pt_mul(pi_a, s));
+    pt_add(pi_c, pt_mul(pib1, r));
+    pt_add(pi_c, pt_neg(pt_mul(delta1, scalar_mul_mod_r(r, s))));
+    if (rk) {
+        HG1XYZZ rdelta1 = from_affine_bytes<HFq>(h.round_delta1);
+        pt_add(pi_c, pt_neg(pt_mul(rdelta1, *rk)));
+    }
+    A = pt_to_affine(pi_a);
+    B = pt_to_affine(pi_b);
+    C = pt_to_affine(pi_c);
+}
+
+int pick_device() {
+    const char* e = getenv("UGB_DEVICE");
+    if (e) return atoi(e);
+    const char* lr = getenv("LOCAL_RANK");
+    if (lr && getenv("UGB_DEVICE_FROM_LOCAL_RANK")) return atoi(lr);
+    return 0;
+}
+
+class ProverBase {
+public:
+    ProverBase(const void* zkey_buffer, unsigned long long zkey_size, bool ultra)
+        : zkey(zkey_buffer, zkey_size, "zkey", 1), hdr(load_zkey_header(zkey, ultra)) {
+        if (!prime_is_bn254_r(hdr.rPrime, hdr.n8r)) throw std::invalid_argument("zkey curve not supported");
+        // the header points (alpha, beta, delta...) are copied: the zkey buffer is only borrowed during create
+        // for everything that goes to HBM, and the reference's file-path variant frees it right after create
+        hdr_copy.assign(zkey.data(2), zkey.data(2) + zkey.size(2));
+        BinFile::Section s{hdr_copy.data(), hdr_copy.size()};
+        rebase(s);
+        dev.reset(new ProverDevice(pick_device(), zkey, hdr));
+    }
+    virtual ~ProverBase() {}
+
+    BinFile zkey;  // only valid during construction (borrowed buffer)
+    ZkeyHeader hdr;
+    std::vector<uint8_t> hdr_copy;
+    std::unique_ptr<ProverDevice> dev;
+    Blinding blinding;
+    bool is_ultra() const { return hdr.ultra; }
+
+protected:
+    void rebase(const BinFile::Section& s) {
+        const uint8_t* old = zkey.data(2);
+        auto mv = [&](const uint8_t*& p) { if (p) p = s.start + (p - old); };
+        mv(hdr.qPrime); mv(hdr.rPrime); mv(hdr.alpha1); mv(hdr.beta1); mv(hdr.beta2); mv(hdr.gamma2);
+        mv(hdr.round_delta1); mv(hdr.round_delta2); mv(hdr.final_delta1); mv(hdr.final_delta2);
+    }
+};
+
+class Groth16Prover : public ProverBase {
+public:
+    Groth16Prover(const void* zkey_buffer, unsigned long long zkey_size) : ProverBase(zkey_buffer, zkey_size, false) {}
+
+    void prove(const void* wtns_buffer, unsigned long long wtns_size, std::string& stringProof, std::string& stringPublic) {
+        BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
+        WtnsHeader wh = load_wtns_header(wtns);
+        if (hdr.nVars != wh.nVars)
+            throw InvalidWitnessLengthException("Invalid witness length. Circuit: " + std::to_string(hdr.nVars) +
+                                                ", witness: " + std::to_string(wh.nVars));
+        if (!prime_is_bn254_r(wh.prime, wh.n8)) throw std::invalid_argument("different wtns curve");
+        if (wtns.size(2) < (uint64_t)hdr.nVars * 32) throw std::range_error("wtns section too short: signals");
+        const uint8_t* w = wtns.data(2);
+        ProofMsms m;
+        dev->prove_groth16(w, m);
+        Scalar r = blinding.fixed ? blinding.r : random_blinding();
+        Scalar s = blinding.fixed ? blinding.s : random_blinding();
+        HG1Affine A, C;
+        HG2Affine B;
+        assemble(hdr, m, r, s, nullptr, A, B, C);
+        stringProof = "{\"pi_a\":" + g1_json(A) + ",\"pi_b\":" + g2_json(B) + ",\"pi_c\":" + g1_json(C) + ",\"protocol\":\"groth16\"}";
+        stringPublic = public_json(w + 32, hdr.nPublic, 0);
+    }
+    unsigned long long proofBufferMinSize() const { return ProofBufferMinSize(); }
+    unsigned long long publicBufferMinSize() const { return PublicBufferMinSize(hdr.nPublic); }
+};
+
+class UltraGrothProver : public ProverBase {
+public:
+    UltraGrothProver(const void* zkey_buffer, unsigned long long zkey_size) : ProverBase(zkey_buffer, zkey_size, true) {}
+
+    void prove(const void* wtns_buffer, unsigned long long wtns_size, std::string& stringProof, std::string& stringPublic) {
+        BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
+        WtnsHeader wh = load_wtns_header(wtns);
+        if (hdr.nVars != wh.nVars)
+            throw InvalidWitnessLengthException("Invalid witness length. Circuit: " + std::to_string(hdr.nVars) +
+                                                ", witness: " + std::to_string(wh.nVars));
+        if (!prime_is_bn254_r(wh.prime, wh.n8)) throw std::invalid_argument("different wtns curve");
+        if (wtns.size(2) < (uint64_t)hdr.nVars * 32) throw std::range_error("wtns section too short: signals");
+        // LookupInfo (src/prover.cpp:287-292, src/ultra_groth.hpp:22-61): four u32 arrays
+        auto u32s = [&](uint32_t id, std::vector<uint32_t>& v) {
+            uint64_t cnt = wtns.size(id) >> 2;
+            v.resize(cnt);
+            if (cnt) memcpy(v.data(), wtns.data(id), cnt * 4);
+        };
+        std::vector<uint32_t> chunks, freqs, widx, pidx;
+        u32s(3, chunks); u32s(4, freqs); u32s(5, widx); u32s(6, pidx);
+        if (widx.size() != pidx.size()) {
+            // the reference iterates wtns_indxs_len entries of both arrays
+            if (pidx.size() < widx.size()) throw std::range_error("wtns push index section shorter than witness index section");
+        }
+        dev->ultra_upload_witness(wtns.data(2));
+        // round 1: commitment = MSM(round_pointsC, round_wtns) + r_k * final_delta1 (src/ultra_groth.cpp:161-184)
+        HG1XYZZ commit;
+        dev->ultra_round_msm(commit);
+        Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
+        HG1XYZZ fdelta1 = from_affine_bytes<HFq>(hdr.final_delta1);
+        pt_add(commit, pt_mul(fdelta1, rk));
+        HG1Affine commit_aff = pt_to_affine(commit);
+        // derive_challenge (src/ultra_groth.cpp:32-58)
+        HFr rand_mont = derive_challenge(commit_aff);
+        dev->ultra_lookup(chunks.data(), (uint32_t)chunks.size(), freqs.data(), (uint32_t)freqs.size(), widx.data(), pidx.data(),
+                          (uint32_t)widx.size(), rand_mont);
+        ProofMsms m;
+        dev->ultra_final_msms(m);
+        Scalar r = blinding.fixed ? blinding.r : random_blinding();
+        Scalar s = blinding.fixed ? blinding.s : random_blinding();
+        HG1Affine A, C;
+        HG2Affine B;
+        assemble(hdr, m, r, s, &rk, A, B, C);
+        stringProof = "{\"pi_a\":" + g1_json(A) + ",\"pi_b\":" + g2_json(B) + ",\"pi_f\":" + g1_json(C) + ",\"pi_r\":" + g1_json(commit_aff) +
+                      ",\"protocol\":\"ultragroth\"}";
+        std::vector<uint8_t> pub((size_t)hdr.nPublic * 32);
+        if (hdr.nPublic) dev->download_witness(pub.data(), 1, hdr.nPublic);
+        stringPublic = public_json(pub.data(), hdr.nPublic, hdr.rand_indx);
+    }
+    unsigned long long proofBufferMinSize() const { return ProofBufferMinSizeUltraGroth(); }
+    unsigned long long publicBufferMinSize() const { return PublicBufferMinSize((unsigned long long)hdr.nPublic - 1); }
+
+    static HFr derive_challenge(const HG1Affine& p) {
+        uint8_t buf[64], digest[32];
+        HFq x = from_mont(p.x), y = from_mont(p.y);
+        for (int i = 0; i < 32; i++) {
+            buf[i] = (uint8_t)(x.v[(31 - i) >> 3] >> (8 * ((31 - i) & 7)));
+            buf[32 + i] = (uint8_t)(y.v[(31 - i) >> 3] >> (8 * ((31 - i) & 7)));
+        }
+        keccak256(buf, 64, digest);
+        HFr raw = HFr::zero();  // digest read big-endian, stored unreduced, then one MMul by R^2
+        for (int i = 0; i < 32; i++) raw.v[(31 - i) >> 3] |= (uint64_t)digest[i] << (8 * ((31 - i) & 7));
+        return to_mont(raw);
+    }
+};
+
+std::vector<uint8_t> read_file(const char* path) {
+    if (!path) throw std::invalid_argument("Null zkey file path");
+    std::ifstream f(path, std::ios::binary | std::ios::ate);
+    if (!f) throw std::system_error(errno, std::generic_category(), std::string("open ") + path);
+    std::streamsize n = f.tellg();
+    f.seekg(0);
+    std::vector<uint8_t> buf((size_t)n);
+    if (n && !f.read((char*)buf.data(), n)) throw std::system_error(errno, std::generic_category(), std::string("read ") + path);
+    return buf;
+}
+
+#define API_TRY try {
+#define API_CATCH_CREATE                                                                                  \
+    }                                                                                                     \
+    catch (std::exception & e) { CopyError(error_msg, error_msg_maxsize, e.what()); return PROVER_ERROR; } \
+    catch (std::exception * e) { CopyError(error_msg, error_msg_maxsize, e->what()); delete e; return PROVER_ERROR; } \
+    catch (...) { CopyError(error_msg, error_msg_maxsize, "unknown error"); return PROVER_ERROR; }         \
+    return PROVER_OK;
+#define API_CATCH_PROVE                                                                                                    \
+    }                                                                                                                      \
+    catch (InvalidWitnessLengthException & e) { CopyError(error_msg, error_msg_maxsize, e.what()); return PROVER_INVALID_WITNESS_LENGTH; } \
+    catch (ShortBufferException & e) { CopyError(error_msg, error_msg_maxsize, e.what()); return PROVER_ERROR_SHORT_BUFFER; } \
+    catch (std::exception & e) { CopyError(error_msg, error_msg_maxsize, e.what()); return PROVER_ERROR; }                   \
+    catch (std::exception * e) { CopyError(error_msg, error_msg_maxsize, e->what()); delete e; return PROVER_ERROR; }        \
+    catch (...) { CopyError(error_msg, error_msg_maxsize, "unknown error"); return PROVER_ERROR; }                           \
+    return PROVER_OK;
+
+template <class P>
+int prover_prove_impl(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, char* proof_buffer,
+                      unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
+                      unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (prover_object == NULL) throw std::invalid_argument("Null prover object");
+    if (wtns_buffer == NULL) throw std::invalid_argument("Null witness buffer");
+    if (proof_buffer == NULL) throw std::invalid_argument("Null proof buffer");
+    if (proof_size == NULL) throw std::invalid_argument("Null proof size");
+    if (public_buffer == NULL) throw std::invalid_argument("Null public buffer");
+    if (public_size == NULL) throw std::invalid_argument("Null public size");
+    P* prover = static_cast<P*>(static_cast<ProverBase*>(prover_object));
+    CheckAndUpdateBufferSizes(prover->proofBufferMinSize(), proof_size, prover->publicBufferMinSize(), public_size, "Minimum");
+    std::string stringProof, stringPublic;
+    prover->prove(wtns_buffer, wtns_size, stringProof, stringPublic);
+    CheckAndUpdateBufferSizes(stringProof.length(), proof_size, stringPublic.length(), public_size, "Required");
+    std::strncpy(proof_buffer, stringProof.c_str(), *proof_size);
+    std::strncpy(public_buffer, stringPublic.c_str(), *public_size);
+    API_CATCH_PROVE
+}
+
+template <class P>
+int prover_create_impl(void** prover_object, const void* zkey_buffer, unsigned long long zkey_size, char* error_msg,
+                       unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (prover_object == NULL) throw std::invalid_argument("Null prover object");
+    if (zkey_buffer == NULL) throw std::invalid_argument("Null zkey buffer");
+    *prover_object = static_cast<ProverBase*>(new P(zkey_buffer, zkey_size));
+    API_CATCH_CREATE
+}
+
+int public_size_impl(const void* zkey_buffer, unsigned long long zkey_size, bool ultra, unsigned long long* public_size, char* error_msg,
+                     unsigned long long error_msg_maxsize) {
+    API_TRY
+    BinFile zkey(zkey_buffer, zkey_size, "zkey", 1);
+    ZkeyHeader h = load_zkey_header(zkey, ultra);
+    *public_size = PublicBufferMinSize(h.nPublic);
+    API_CATCH_CREATE
+}
+
+}  // namespace
+
+extern "C" {
+
+int groth16_public_size_for_zkey_buf(const void* zkey_buffer, unsigned long long zkey_size, unsigned long long* public_size, char* error_msg,
+                                     unsigned long long error_msg_maxsize) {
+    return public_size_impl(zkey_buffer, zkey_size, false, public_size, error_msg, error_msg_maxsize);
+}
+int ultra_groth_public_size_for_zkey_buf(const void* zkey_buffer, unsigned long long zkey_size, unsigned long long* public_size,
+                                         char* error_msg, unsigned long long error_msg_maxsize) {
+    return public_size_impl(zkey_buffer, zkey_size, true, public_size, error_msg, error_msg_maxsize);
+}
+int groth16_public_size_for_zkey_file(const char* zkey_fname, unsigned long long* public_size, char* error_msg,
+                                      unsigned long long error_msg_maxsize) {
+    API_TRY
+    std::vector<uint8_t> buf = read_file(zkey_fname);
+    BinFile zkey(buf.data(), buf.size(), "zkey", 1);
+    *public_size = PublicBufferMinSize(load_zkey_header(zkey, false).nPublic);
+    API_CATCH_CREATE
+}
+int ultra_groth_public_size_for_zkey_file(const char* zkey_fname, unsigned long long* public_size, char* error_msg,
+                                          unsigned long long error_msg_maxsize) {
+    API_TRY
+    std::vector<uint8_t> buf = read_file(zkey_fname);
+    BinFile zkey(buf.data(), buf.size(), "zkey", 1);
+    *public_size = PublicBufferMinSize(load_zkey_header(zkey, true).nPublic);
+    API_CATCH_CREATE
+}
+
+void groth16_proof_size(unsigned long long* proof_size) { *proof_size = ProofBufferMinSize(); }
+void ultra_groth_proof_size(unsigned long long* proof_size) { *proof_size = ProofBufferMinSizeUltraGroth(); }
+
+int groth16_prover_create(void** prover_object, const void* zkey_buffer, unsigned long long zkey_size, char* error_msg,
+                          unsigned long long error_msg_maxsize) {
+    return prover_create_impl<Groth16Prover>(prover_object, zkey_buffer, zkey_size, error_msg, error_msg_maxsize);
+}
+int ultra_groth_prover_create(void** prover_object, const void* zkey_buffer, unsigned long long zkey_size, char* error_msg,
+                              unsigned long long error_msg_maxsize) {
+    return prover_create_impl<UltraGrothProver>(prover_object, zkey_buffer, zkey_size, error_msg, error_msg_maxsize);
+}
+int groth16_prover_create_zkey_file(void** prover_object, const char* zkey_file_path, char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (prover_object == NULL) throw std::invalid_argument("Null prover object");
+    std::vector<uint8_t> buf = read_file(zkey_file_path);
+    *prover_object = static_cast<ProverBase*>(new Groth16Prover(buf.data(), buf.size()));
+    API_CATCH_CREATE
+}
+int ultra_groth_prover_create_zkey_file(void** prover_object, const char* zkey_file_path, char* error_msg,
+                                        unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (prover_object == NULL) throw std::invalid_argument("Null prover object");
+    std::vector<uint8_t> buf = read_file(zkey_file_path);
+    *prover_object = static_cast<ProverBase*>(new UltraGrothProver(buf.data(), buf.size()));
+    API_CATCH_CREATE
+}
+
+int groth16_prover_prove(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, char* proof_buffer,
+                         unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
+                         unsigned long long error_msg_maxsize) {
+    return prover_prove_impl<Groth16Prover>(prover_object, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size,
+                                            error_msg, error_msg_maxsize);
+}
+int ultra_groth_prover_prove(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, char* proof_buffer,
+                             unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
+                             unsigned long long error_msg_maxsize) {
+    return prover_prove_impl<UltraGrothProver>(prover_object, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size,
+                                               error_msg, error_msg_maxsize);
+}
+
+void groth16_prover_destroy(void* prover_object) {
+    if (prover_object != NULL) delete static_cast<ProverBase*>(prover_object);
+}
+void ultra_groth_prover_destroy(void* prover_object) {
+    if (prover_object != NULL) delete static_cast<ProverBase*>(prover_object);
+}
+
+int groth16_prover(const void* zkey_buffer, unsigned long long zkey_size, const void* wtns_buffer, unsigned long long wtns_size,
+                   char* proof_buffer, unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
+                   unsigned long long error_msg_maxsize) {
+    void* prover = NULL;
+    int error = groth16_prover_create(&prover, zkey_buffer, zkey_size, error_msg, error_msg_maxsize);
+    if (error != PROVER_OK) return error;
+    error = groth16_prover_prove(prover, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
+                                 error_msg_maxsize);
+    groth16_prover_destroy(prover);
+    return error;
+}
+int ultra_groth_prover(const void* zkey_buffer, unsigned long long zkey_size, const void* wtns_buffer, unsigned long long wtns_size,
+                       char* proof_buffer, unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size,
+                       char* error_msg, unsigned long long error_msg_maxsize) {
+    void* prover = NULL;
+    int error = ultra_groth_prover_create(&prover, zkey_buffer, zkey_size, error_msg, error_msg_maxsize);
+    if (error != PROVER_OK) return error;
+    error = ultra_groth_prover_prove(prover, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
+                                     error_msg_maxsize);
+    ultra_groth_prover_destroy(prover);
+    return error;
+}
+int groth16_prover_zkey_file(const char* zkey_file_path, const void* wtns_buffer, unsigned long long wtns_size, char* proof_buffer,
+                             unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
+                             unsigned long long error_msg_maxsize) {
+    void* prover = NULL;
+    int error = groth16_prover_create_zkey_file(&prover, zkey_file_path, error_msg, error_msg_maxsize);
+    if (error != PROVER_OK) return error;
+    error = groth16_prover_prove(prover, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
+                                 error_msg_maxsize);
+    groth16_prover_destroy(prover);
+    return error;
+}
+int ultra_groth_prover_zkey_file(const char* zkey_file_path, const void* wtns_buffer, unsigned long long wtns_size, char* proof_buffer,
+                                 unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
+                                 unsigned long long error_msg_maxsize) {
+    void* prover = NULL;
+    int error = ultra_groth_prover_create_zkey_file(&prover, zkey_file_path, error_msg, error_msg_maxsize);
+    if (error != PROVER_OK) return error;
+    error = ultra_groth_prover_prove(prover, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
+                                     error_msg_maxsize);
+    ultra_groth_prover_destroy(prover);
+    return error;
+}
+
+// ---- extensions declared in include/ultragroth_b200.h ---------------------------------------------
+int ugb_prover_set_blinding(void* prover_object, const void* r32, const void* s32, const void* rk32) {
+    if (!prover_object) return UGB_ERROR;
+    ProverBase* p = static_cast<ProverBase*>(prover_object);
+    if (!r32 || !s32) { p->blinding.fixed = false; return UGB_OK; }
+    p->blinding.fixed = true;
+    memcpy(&p->blinding.r, r32, 32);
+    memcpy(&p->blinding.s, s32, 32);
+    if (rk32) memcpy(&p->blinding.rk, rk32, 32); else memset(&p->blinding.rk, 0, 32);
+    return UGB_OK;
+}
+int ugb_prover_last_h(void* prover_object, void* h_out, uint64_t bytes) {
+    if (!prover_object) return UGB_ERROR;
+    try {
+        ProverBase* p = static_cast<ProverBase*>(prover_object);
+        std::vector<uint8_t> h;
+        p->dev->download_h(h);
+        memcpy(h_out, h.data(), std::min<uint64_t>(bytes, h.size()));
+    } catch (...) { return UGB_ERROR; }
+    return UGB_OK;
+}
+int ugb_prover_set_timing(void* prover_object, int enable) {
+    if (!prover_object) return UGB_ERROR;
+    static_cast<ProverBase*>(prover_object)->dev->timing = enable != 0;
+    return UGB_OK;
+}
+int ugb_prover_last_times(void* prover_object, float* out, int count) {
+    if (!prover_object) return UGB_ERROR;
+    const StageTimes& t = static_cast<ProverBase*>(prover_object)->dev->last_times;
+    const float v[] = {t.upload, t.round, t.lookup, t.sort_w, t.msm_a, t.msm_b1, t.msm_b2, t.msm_c, t.spmv, t.intt, t.ntt, t.hfinal, t.sort_h, t.msm_h, t.total};
+    for (int i = 0; i < count && i < (int)(sizeof(v) / sizeof(v[0])); i++) out[i] = v[i];
+    return UGB_OK;
+}
+uint64_t ugb_prover_kernel_launches(void* prover_object) {
+    if (!prover_object) return 0;
+    return static_cast<ProverBase*>(prover_object)->dev->ctx().kernel_launches;
+}
+void* ugb_prover_stream(void* prover_object) {
+    if (!prover_object) return nullptr;
+    return (void*)static_cast<ProverBase*>(prover_object)->dev->ctx().stream;
+}
+
+}  // extern "C"

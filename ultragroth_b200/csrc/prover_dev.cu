@@ -1,0 +1,385 @@
+// Device side of the Groth16 / UltraGroth prover: the data-parallel loops of
+// Groth16::Prover::prove (src/groth16.cpp:48-154) and UltraGroth's rounds (src/ultra_groth.cpp:62-106,
+// 161-335) as sm_100a kernels over HBM-resident zkey data.
+#include "prover_dev.hpp"
+
+#include <algorithm>
+#include <cstdlib>
+
+#include "curve.cuh"
+#include "memops.cuh"
+
+namespace ug {
+
+// ---- a[c] = sum_{A row c} w[s]*coef, b[c] likewise, c[c] = a[c]*b[c]   (src/groth16.cpp:70-108) ----
+// The reference scatters coefficient records under 1024 mutex stripes; here the records were
+// bucketed by (matrix, row) at upload time, so one thread owns one constraint row: no atomics.
+// coef holds value*R^2 (zkey convention), so fp_mul(raw witness, coef) is the Montgomery product.
+__global__ void __launch_bounds__(256) k_spmv_abc(const uint32_t* __restrict__ row_ptr, const uint32_t* __restrict__ sig,
+                                                  const Fr* __restrict__ coef, const Fr* __restrict__ w, uint32_t n,
+                                                  Fr* __restrict__ a, Fr* __restrict__ b, Fr* __restrict__ c) {
+    for (uint32_t row = blockIdx.x * blockDim.x + threadIdx.x; row < n; row += gridDim.x * blockDim.x) {
+        Fr acc[2];
+#pragma unroll
+        for (int m = 0; m < 2; m++) {
+            acc[m] = Fr::zero();
+            uint32_t lo = row_ptr[m * n + row], hi = row_ptr[m * n + row + 1];
+            for (uint32_t k = lo; k < hi; k++) {
+                Fr wv = ld_nc(&w[sig[k]]);
+                acc[m] = fp_add(acc[m], fp_mul(wv, ld_nc(&coef[k])));
+            }
+        }
+        st_g(&a[row], acc[0]);
+        st_g(&b[row], acc[1]);
+        st_g(&c[row], fp_mul(acc[0], acc[1]));
+    }
+}
+
+// h[i] = fromMontgomery(a[i]*b[i] - c[i])   (src/groth16.cpp:142-148), written over a
+__global__ void __launch_bounds__(256) k_h_final(Fr* __restrict__ a, const Fr* __restrict__ b, const Fr* __restrict__ c, uint32_t n) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        Fr x = fp_mul(ld_g(&a[i]), ld_g(&b[i]));
+        x = fp_sub(x, ld_g(&c[i]));
+        st_g(&a[i], fp_from_mont(x));
+    }
+}
+
+// ---- compute_lookup (src/ultra_groth.cpp:62-106) ----
+// inv2[i] = fromMont((i + rand)^-1), prod[i] = fromMont(freq[i] * (i + rand)^-1): the reference runs one
+// GMP mpz_invert per table entry; here every thread inverts a run of LOOKUP_RUN entries with
+// Montgomery's trick (one Fermat inversion + 3 products per entry).
+constexpr int LOOKUP_RUN = 8;
+
+__global__ void __launch_bounds__(128) k_lookup_inverses(const uint32_t* __restrict__ freqs, uint32_t lookup_size, Fr rand_mont,
+                                                         Fr* __restrict__ inv2, Fr* __restrict__ prod) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t base = t * LOOKUP_RUN;
+    if (base >= lookup_size) return;
+    const uint32_t cnt = min((uint32_t)LOOKUP_RUN, lookup_size - base);
+    Fr val[LOOKUP_RUN], pre[LOOKUP_RUN];
+    Fr acc = Fr::one();
+    for (uint32_t k = 0; k < cnt; k++) {
+        Fr iv = Fr::zero();
+        iv.v[0] = base + k;
+        val[k] = fp_add(fp_to_mont(iv), rand_mont);
+        pre[k] = acc;
+        // a zero (i + rand == 0) has no inverse; mpz_invert leaves 0 there, keep it out of the product
+        if (!val[k].is_zero()) acc = fp_mul(acc, val[k]);
+    }
+    Fr inv = fp_inv(acc);
+    for (int k = (int)cnt - 1; k >= 0; k--) {
+        Fr r = Fr::zero();
+        if (!val[k].is_zero()) {
+            r = fp_mul(inv, pre[k]);
+            inv = fp_mul(inv, val[k]);
+        }
+        Fr f = Fr::zero();
+        f.v[0] = freqs[base + k];
+        st_g(&inv2[base + k], fp_from_mont(r));
+        st_g(&prod[base + k], fp_from_mont(fp_mul(fp_to_mont(f), r)));
+    }
+}
+
+// signals[wtns_idx[k]] = push_vector[push_idx[k]], push_vector = [rand | inv2[chunks[*]] | inv2 | prod]
+__global__ void __launch_bounds__(256) k_lookup_push(const uint32_t* __restrict__ wtns_idx, const uint32_t* __restrict__ push_idx,
+                                                     uint32_t count, const uint32_t* __restrict__ chunks, uint32_t chunks_total,
+                                                     uint32_t lookup_size, Fr rand_raw, const Fr* __restrict__ inv2,
+                                                     const Fr* __restrict__ prod, Fr* __restrict__ signals) {
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
+        uint32_t p = push_idx[k];
+        Fr v;
+        if (p == 0) v = rand_raw;
+        else if (p <= chunks_total) v = ld_g(&inv2[chunks[p - 1]]);
+        else if (p <= chunks_total + lookup_size) v = ld_g(&inv2[p - 1 - chunks_total]);
+        else v = ld_g(&prod[p - 1 - chunks_total - lookup_size]);
+        st_g(&signals[wtns_idx[k]], v);
+    }
+}
+
+// ---- upload helpers -------------------------------------------------------------------------------
+static void* dev_alloc(size_t bytes) {
+    void* p = nullptr;
+    UG_CUDA_CHECK(cudaMalloc(&p, std::max<size_t>(bytes, 16)));
+    return p;
+}
+
+static void* upload(DeviceCtx& ctx, const void* src, size_t bytes) {
+    void* p = dev_alloc(bytes);
+    if (bytes) UG_CUDA_CHECK(cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, ctx.stream));
+    return p;
+}
+
+static int ilog2_exact(uint32_t n) {
+    int k = 0;
+    while ((1u << k) < n) k++;
+    if ((1u << k) != n) throw std::invalid_argument("zkey domain size is not a power of two");
+    return k;
+}
+
+ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
+    : nVars(h.nVars), nPublic(h.nPublic), domainSize(h.domainSize), ultra_(h.ultra) {
+    if (h.n8q != 32 || h.n8r != 32) throw std::invalid_argument("zkey field size not supported");
+    logn = ilog2_exact(domainSize);
+    if (nPublic + 1 > nVars) throw std::invalid_argument("zkey header is inconsistent (nPublic >= nVars)");
+    ctx_.reset(new DeviceCtx(device));
+    tabs_.reset(new NttTables(*ctx_));
+    DeviceCtx& ctx = *ctx_;
+    ctx.activate();
+    timing = getenv("UGB_TIMING") != nullptr;
+
+    auto need = [&](uint32_t id, uint64_t bytes, const char* what) {
+        if (zkey.size(id) < bytes) throw std::range_error(std::string("zkey section too short: ") + what);
+    };
+    need(5, (uint64_t)nVars * 64, "pointsA");
+    need(6, (uint64_t)nVars * 64, "pointsB1");
+    need(7, (uint64_t)nVars * 128, "pointsB2");
+    A_ = upload(ctx, zkey.data(5), (size_t)nVars * 64);
+    B1_ = upload(ctx, zkey.data(6), (size_t)nVars * 64);
+    B2_ = upload(ctx, zkey.data(7), (size_t)nVars * 128);
+    std::vector<uint8_t> cfull;  // must outlive the async copy
+    if (!ultra_) {
+        const uint32_t nc = nVars - nPublic - 1;
+        need(8, (uint64_t)nc * 64, "pointsC");
+        need(9, (uint64_t)domainSize * 64, "pointsH");
+        // C pairs with witness[nPublic+1 ..] (src/groth16.cpp:64): pad with points at infinity so that the
+        // C MSM reuses the sorted digits of the full witness
+        C_ = dev_alloc((size_t)nVars * 64);
+        UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, (size_t)(nPublic + 1) * 64, ctx.stream));
+        if (nc) UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)C_ + (size_t)(nPublic + 1) * 64, zkey.data(8), (size_t)nc * 64, cudaMemcpyHostToDevice, ctx.stream));
+        c_shares_witness_sort_ = true;
+        H_ = upload(ctx, zkey.data(9), (size_t)domainSize * 64);
+    } else {
+        n_c1_ = h.num_indexes_c1;
+        n_c2_ = h.num_indexes_c2;
+        need(8, (uint64_t)n_c1_ * 64, "round pointsC");
+        need(9, (uint64_t)n_c2_ * 64, "final pointsC");
+        need(10, (uint64_t)n_c1_ * 4, "round indexes");
+        need(11, (uint64_t)n_c2_ * 4, "final indexes");
+        need(12, (uint64_t)domainSize * 64, "pointsH");
+        const uint32_t* i1 = (const uint32_t*)zkey.data(10);
+        const uint32_t* i2 = (const uint32_t*)zkey.data(11);
+        for (uint32_t i = 0; i < n_c1_; i++) { uint32_t v; memcpy(&v, i1 + i, 4); if (v >= nVars) throw std::range_error("round index out of range"); }
+        bool unique = true;
+        {
+            std::vector<bool> seen(nVars, false);
+            for (uint32_t i = 0; i < n_c2_; i++) {
+                uint32_t v; memcpy(&v, i2 + i, 4);
+                if (v >= nVars) throw std::range_error("final round index out of range");
+                if (seen[v]) unique = false;
+                seen[v] = true;
+            }
+        }
+        C1_ = upload(ctx, zkey.data(8), (size_t)n_c1_ * 64);
+        idx_c1_ = (uint32_t*)upload(ctx, zkey.data(10), (size_t)n_c1_ * 4);
+        idx_c2_ = (uint32_t*)upload(ctx, zkey.data(11), (size_t)n_c2_ * 4);
+        if (unique) {
+            // final_wtns[i] = wtns[final_idx[i]] (src/ultra_groth.cpp:439-445): place C2[i] at slot final_idx[i]
+            // of an nVars-long array of points at infinity, so the final C MSM shares the witness digits
+            cfull.assign((size_t)nVars * 64, 0);
+            const uint8_t* c2 = zkey.data(9);
+            for (uint32_t i = 0; i < n_c2_; i++) { uint32_t v; memcpy(&v, i2 + i, 4); memcpy(&cfull[(size_t)v * 64], c2 + (size_t)i * 64, 64); }
+            C_ = upload(ctx, cfull.data(), cfull.size());
+            c_shares_witness_sort_ = true;
+        } else {
+            C_ = upload(ctx, zkey.data(9), (size_t)n_c2_ * 64);
+            c_shares_witness_sort_ = false;
+        }
+        H_ = upload(ctx, zkey.data(12), (size_t)domainSize * 64);
+    }
+
+    // coefficient records {u32 m, u32 c, u32 s, Fr coef} packed(1) after a u32 count (src/groth16.cpp:38,
+    // src/groth16.hpp:42-50) -> CSR by (m, c)
+    {
+        const uint8_t* sec = zkey.data(4);
+        uint64_t sec_size = zkey.size(4);
+        if (sec_size < 4) throw std::range_error("zkey section too short: coefs");
+        uint64_t cnt = std::min<uint64_t>(h.nCoefs, (sec_size - 4) / 44);
+        const uint8_t* rec = sec + 4;
+        nCoefs_ = cnt;
+        const uint32_t n = domainSize;
+        std::vector<uint32_t> rp((size_t)2 * n + 1, 0);
+        for (uint64_t k = 0; k < cnt; k++) {
+            uint32_t m, c, s;
+            memcpy(&m, rec + k * 44, 4); memcpy(&c, rec + k * 44 + 4, 4); memcpy(&s, rec + k * 44 + 8, 4);
+            if (m > 1 || c >= n || s >= nVars) throw std::range_error("zkey coefficient record out of range");
+            rp[(size_t)m * n + c + 1]++;
+        }
+        for (size_t i = 0; i < (size_t)2 * n; i++) rp[i + 1] += rp[i];
+        std::vector<uint32_t> cur(rp.begin(), rp.end() - 1);
+        std::vector<uint32_t> sig(cnt);
+        std::vector<uint8_t> val(cnt * 32);
+        for (uint64_t k = 0; k < cnt; k++) {
+            uint32_t m, c, s;
+            memcpy(&m, rec + k * 44, 4); memcpy(&c, rec + k * 44 + 4, 4); memcpy(&s, rec + k * 44 + 8, 4);
+            uint32_t pos = cur[(size_t)m * n + c]++;
+            sig[pos] = s;
+            memcpy(&val[(size_t)pos * 32], rec + k * 44 + 12, 32);
+        }
+        row_ptr_ = (uint32_t*)upload(ctx, rp.data(), rp.size() * 4);
+        coef_sig_ = (uint32_t*)upload(ctx, sig.data(), sig.size() * 4);
+        coef_val_ = upload(ctx, val.data(), val.size());
+        UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+    }
+    w_ = dev_alloc((size_t)nVars * 32);
+    a_ = dev_alloc((size_t)domainSize * 32);
+    b_ = dev_alloc((size_t)domainSize * 32);
+    c_ = dev_alloc((size_t)domainSize * 32);
+    // twiddles resident before the first proof
+    tabs_->stage_roots(false);
+    tabs_->stage_roots(true);
+    if (logn > 0) {
+        tabs_->coset_inv_bitrev(logn);
+        if (logn > 12) tabs_->full_roots(logn);
+    }
+    ev_.resize(16);
+    for (auto& e : ev_) UG_CUDA_CHECK(cudaEventCreate(&e));
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+}
+
+ProverDevice::~ProverDevice() {
+    cudaSetDevice(ctx_->device);
+    cudaStreamSynchronize(ctx_->stream);
+    for (void* p : {A_, B1_, B2_, C_, H_, C1_, (void*)idx_c1_, (void*)idx_c2_, (void*)row_ptr_, (void*)coef_sig_, coef_val_, w_, a_, b_, c_})
+        if (p) cudaFree(p);
+    for (auto& e : ev_) cudaEventDestroy(e);
+}
+
+void ProverDevice::download_h(std::vector<uint8_t>& out) {
+    ctx_->activate();
+    out.resize((size_t)domainSize * 32);
+    UG_CUDA_CHECK(cudaMemcpyAsync(out.data(), a_, out.size(), cudaMemcpyDeviceToHost, ctx_->stream));
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx_->stream));
+}
+
+void ProverDevice::download_witness(uint8_t* dst, uint64_t first, uint64_t count) {
+    ctx_->activate();
+    UG_CUDA_CHECK(cudaMemcpyAsync(dst, (uint8_t*)w_ + first * 32, count * 32, cudaMemcpyDeviceToHost, ctx_->stream));
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx_->stream));
+}
+
+// Everything from the (device-resident) witness to the five MSM results.
+void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
+    DeviceCtx& ctx = *ctx_;
+    const uint32_t n = domainSize;
+    int e = 0;
+    auto mark = [&]() { if (timing) UG_CUDA_CHECK(cudaEventRecord(ev_[e++], ctx.stream)); };
+    mark();  // 0
+    // the four witness MSMs share one digit sort (src/groth16.cpp:53-64 all read the same scalars)
+    MsmDigits dw;
+    msm_sort_digits(ctx, (const uint8_t*)w_, nullptr, nVars, 0, "w", dw);
+    mark();  // 1
+    msm_g1_launch(ctx, A_, dw, "a");
+    mark();  // 2
+    msm_g1_launch(ctx, B1_, dw, "b1");
+    mark();  // 3
+    msm_g2_launch(ctx, B2_, dw, "b2");
+    mark();  // 4
+    MsmDigits dc;
+    if (c_shares_witness_sort_) {
+        msm_g1_launch(ctx, C_, dw, "c");
+    } else {
+        msm_sort_digits(ctx, (const uint8_t*)w_, idx_c2_, n_c2_, 0, "cidx", dc);
+        msm_g1_launch(ctx, C_, dc, "c");
+    }
+    mark();  // 5
+    // H pipeline
+    int blocks = (int)std::min<uint64_t>(((uint64_t)n + 255) / 256, (uint64_t)ctx.sm_count * 8);
+    k_spmv_abc<<<blocks, 256, 0, ctx.stream>>>(row_ptr_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, n, (Fr*)a_, (Fr*)b_, (Fr*)c_);
+    UG_LAUNCH_CHECK(ctx);
+    mark();  // 6
+    Fr* vecs[3] = {(Fr*)a_, (Fr*)b_, (Fr*)c_};
+    // ifft + coset shift (+ 1/n) fused, output bit-reversed; then fft from bit-reversed to natural
+    ntt_run(ctx, *tabs_, vecs, 3, logn, NTT_NATURAL_TO_BITREV, true, tabs_->coset_inv_bitrev(logn), nullptr);
+    mark();  // 7
+    ntt_run(ctx, *tabs_, vecs, 3, logn, NTT_BITREV_TO_NATURAL, false, nullptr, nullptr);
+    mark();  // 8
+    k_h_final<<<blocks, 256, 0, ctx.stream>>>((Fr*)a_, (const Fr*)b_, (const Fr*)c_, n);
+    UG_LAUNCH_CHECK(ctx);
+    mark();  // 9
+    MsmDigits dh;
+    msm_sort_digits(ctx, (const uint8_t*)a_, nullptr, n, 0, "h", dh);
+    mark();  // 10
+    msm_g1_launch(ctx, H_, dh, "h");
+    mark();  // 11
+    msm_g1_finish(ctx, dw, "a", &out.a);
+    msm_g1_finish(ctx, dw, "b1", &out.b1);
+    msm_g2_finish(ctx, dw, "b2", &out.b2);
+    msm_g1_finish(ctx, c_shares_witness_sort_ ? dw : dc, "c", &out.c);
+    msm_g1_finish(ctx, dh, "h", &out.h);
+    if (timing) {
+        UG_CUDA_CHECK(cudaEventSynchronize(ev_[11]));
+        float* dst[] = {&last_times.sort_w, &last_times.msm_a, &last_times.msm_b1, &last_times.msm_b2, &last_times.msm_c, &last_times.spmv,
+                        &last_times.intt, &last_times.ntt, &last_times.hfinal, &last_times.sort_h, &last_times.msm_h};
+        for (int i = 0; i < 11; i++) UG_CUDA_CHECK(cudaEventElapsedTime(dst[i], ev_[i], ev_[i + 1]));
+        UG_CUDA_CHECK(cudaEventElapsedTime(&last_times.total, ev_[0], ev_[11]));
+    }
+}
+
+void ProverDevice::prove_groth16(const uint8_t* witness, ProofMsms& out) {
+    DeviceCtx& ctx = *ctx_;
+    ctx.activate();
+    UG_CUDA_CHECK(cudaMemcpyAsync(w_, witness, (size_t)nVars * 32, cudaMemcpyHostToDevice, ctx.stream));
+    h_pipeline_and_msms(out, false);
+}
+
+void ProverDevice::ultra_upload_witness(const uint8_t* witness) {
+    ctx_->activate();
+    UG_CUDA_CHECK(cudaMemcpyAsync(w_, witness, (size_t)nVars * 32, cudaMemcpyHostToDevice, ctx_->stream));
+}
+
+void ProverDevice::ultra_round_msm(HG1XYZZ& out) {
+    DeviceCtx& ctx = *ctx_;
+    ctx.activate();
+    // round_wtns[i] = wtns[round_indexes[i]] (src/ultra_groth.cpp:415-419) folded into the scalar fetch
+    MsmDigits d;
+    msm_sort_digits(ctx, (const uint8_t*)w_, idx_c1_, n_c1_, 0, "round", d);
+    msm_g1_launch(ctx, C1_, d, "round");
+    msm_g1_finish(ctx, d, "round", &out);
+}
+
+void ProverDevice::ultra_lookup(const uint32_t* chunks, uint32_t chunks_len, const uint32_t* freqs, uint32_t freqs_len,
+                                const uint32_t* wtns_idx, const uint32_t* push_idx, uint32_t idx_len, const HFr& rand_mont) {
+    DeviceCtx& ctx = *ctx_;
+    ctx.activate();
+    // bounds (the reference trusts the file; out-of-range indices would be wild writes there)
+    for (uint32_t i = 0; i < chunks_len; i++) if (chunks[i] >= freqs_len) throw std::range_error("lookup chunk index out of range");
+    const uint64_t push_len = 1ull + chunks_len + 2ull * freqs_len;
+    for (uint32_t i = 0; i < idx_len; i++) {
+        if (wtns_idx[i] >= nVars) throw std::range_error("lookup witness index out of range");
+        if (push_idx[i] >= push_len) throw std::range_error("lookup push index out of range");
+    }
+    uint32_t* d_chunks = (uint32_t*)ctx.workspace("lk.chunks", (size_t)chunks_len * 4 + 16);
+    uint32_t* d_freqs = (uint32_t*)ctx.workspace("lk.freqs", (size_t)freqs_len * 4 + 16);
+    uint32_t* d_widx = (uint32_t*)ctx.workspace("lk.widx", (size_t)idx_len * 4 + 16);
+    uint32_t* d_pidx = (uint32_t*)ctx.workspace("lk.pidx", (size_t)idx_len * 4 + 16);
+    Fr* d_inv2 = (Fr*)ctx.workspace("lk.inv2", (size_t)freqs_len * 32 + 32);
+    Fr* d_prod = (Fr*)ctx.workspace("lk.prod", (size_t)freqs_len * 32 + 32);
+    if (chunks_len) UG_CUDA_CHECK(cudaMemcpyAsync(d_chunks, chunks, (size_t)chunks_len * 4, cudaMemcpyHostToDevice, ctx.stream));
+    if (freqs_len) UG_CUDA_CHECK(cudaMemcpyAsync(d_freqs, freqs, (size_t)freqs_len * 4, cudaMemcpyHostToDevice, ctx.stream));
+    if (idx_len) {
+        UG_CUDA_CHECK(cudaMemcpyAsync(d_widx, wtns_idx, (size_t)idx_len * 4, cudaMemcpyHostToDevice, ctx.stream));
+        UG_CUDA_CHECK(cudaMemcpyAsync(d_pidx, push_idx, (size_t)idx_len * 4, cudaMemcpyHostToDevice, ctx.stream));
+    }
+    Fr rm, rr;
+    memcpy(&rm, &rand_mont, 32);
+    HFr raw = from_mont(rand_mont);
+    memcpy(&rr, &raw, 32);
+    if (freqs_len) {
+        uint32_t threads = (freqs_len + LOOKUP_RUN - 1) / LOOKUP_RUN;
+        k_lookup_inverses<<<(threads + 127) / 128, 128, 0, ctx.stream>>>(d_freqs, freqs_len, rm, d_inv2, d_prod);
+        UG_LAUNCH_CHECK(ctx);
+    }
+    if (idx_len) {
+        int blocks = (int)std::min<uint64_t>(((uint64_t)idx_len + 255) / 256, (uint64_t)ctx.sm_count * 8);
+        k_lookup_push<<<blocks, 256, 0, ctx.stream>>>(d_widx, d_pidx, idx_len, d_chunks, chunks_len, freqs_len, rr, d_inv2, d_prod, (Fr*)w_);
+        UG_LAUNCH_CHECK(ctx);
+    }
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));  // host index arrays are borrowed
+}
+
+void ProverDevice::ultra_final_msms(ProofMsms& out) {
+    ctx_->activate();
+    h_pipeline_and_msms(out, true);
+}
+
+}  // namespace ug

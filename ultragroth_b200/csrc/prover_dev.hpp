@@ -1,0 +1,77 @@
+// Device-resident prover state: everything Groth16::Prover / UltraGroth::Prover keep as raw zkey
+// pointers (src/groth16.hpp:74-114, src/ultra_groth.hpp:108-206) lives here in HBM instead, uploaded
+// once at *_prover_create (north star item 4: bases and twiddles stay resident across proofs).
+#pragma once
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "device.hpp"
+#include "hostio.hpp"
+#include "msm.hpp"
+#include "ntt.hpp"
+
+namespace ug {
+
+// The MSM results of one proof, as XYZZ partial sums on the host (one per shard when several GPUs
+// hold disjoint point ranges; the caller adds them up).
+struct ProofMsms {
+    HG1XYZZ a, b1, c, h, round_c;
+    HG2XYZZ b2;
+};
+
+struct StageTimes {  // milliseconds of device time per stage of the last proof (CUDA events)
+    float upload = 0, round = 0, lookup = 0, sort_w = 0, msm_a = 0, msm_b1 = 0, msm_b2 = 0, msm_c = 0, spmv = 0, intt = 0, ntt = 0,
+          hfinal = 0, sort_h = 0, msm_h = 0, total = 0;
+};
+
+class ProverDevice {
+public:
+    // point range [lo, hi) of every base array kept by this device; full = does the H pipeline
+    ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& hdr);
+    ~ProverDevice();
+
+    DeviceCtx& ctx() { return *ctx_; }
+    NttTables& tables() { return *tabs_; }
+
+    // ---- Groth16 (src/groth16.cpp:48-203 up to the blinding) ----
+    // witness: nVars raw 32-byte scalars on the host
+    void prove_groth16(const uint8_t* witness, ProofMsms& out);
+
+    // ---- UltraGroth (src/ultra_groth.cpp:401-462) ----
+    void ultra_upload_witness(const uint8_t* witness);
+    void ultra_round_msm(HG1XYZZ& out);                                   // execute_round's MSM (:168)
+    void ultra_lookup(const uint32_t* chunks, uint32_t chunks_len, const uint32_t* freqs, uint32_t freqs_len, const uint32_t* wtns_idx,
+                      const uint32_t* push_idx, uint32_t idx_len, const HFr& rand_mont);  // compute_lookup (:62-106)
+    void ultra_final_msms(ProofMsms& out);                                // execute_final_round's MSMs + H
+    void download_witness(uint8_t* dst, uint64_t first, uint64_t count);  // signals after the lookup fill
+
+    // debug / parity taps
+    void download_h(std::vector<uint8_t>& out);  // the H-MSM scalars of the last proof (canonical integers)
+    StageTimes last_times;
+    bool timing = false;
+
+    uint32_t nVars, nPublic, domainSize;
+    int logn;
+
+private:
+    void h_pipeline_and_msms(ProofMsms& out, bool ultra);
+    std::unique_ptr<DeviceCtx> ctx_;
+    std::unique_ptr<NttTables> tabs_;
+    bool ultra_;
+    uint32_t n_c1_ = 0, n_c2_ = 0;
+    // bases
+    void *A_ = nullptr, *B1_ = nullptr, *B2_ = nullptr, *C_ = nullptr, *H_ = nullptr, *C1_ = nullptr;
+    bool c_shares_witness_sort_ = false;
+    uint32_t *idx_c1_ = nullptr, *idx_c2_ = nullptr;
+    // coefficient matrix, CSR by (matrix, row)
+    uint32_t* row_ptr_ = nullptr;  // [2n + 1]
+    uint32_t* coef_sig_ = nullptr;
+    void* coef_val_ = nullptr;
+    uint64_t nCoefs_ = 0;
+    // per-proof buffers
+    void *w_ = nullptr, *a_ = nullptr, *b_ = nullptr, *c_ = nullptr;
+    std::vector<cudaEvent_t> ev_;
+};
+
+}  // namespace ug

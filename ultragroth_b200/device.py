@@ -92,3 +92,17 @@ class Context:
         check(fn(self.handle, bases.ptr, scalars.ptr + 32 * scalar_offset, index.ptr if index is not None else None,
                  n, window_bits, out))
         return out.raw
+
+    def ntt(self, data: DeviceArray, logn, inverse=False):
+        """FFT<Fr>::fft / ifft: natural order in and out, in place."""
+        check(lib().ugb_ntt(self.handle, data.ptr, logn, 1 if inverse else 0))
+
+    def coset_transform(self, vecs, logn):
+        """ifft -> multiply by omega_2n^i -> fft on up to three vectors (src/groth16.cpp:110-140)."""
+        arr = (ctypes.c_void_p * len(vecs))(*[v.ptr for v in vecs])
+        check(lib().ugb_coset_transform(self.handle, arr, len(vecs), logn))
+
+    def bench_int_pipe(self, kind):
+        v = ctypes.c_double()
+        check(lib().ugb_bench_int_pipe(self.handle, kind, ctypes.byref(v)))
+        return v.value
