@@ -103,6 +103,19 @@ void* ugb_prover_stream(void* prover_object);
  * products (4 chains per thread).  Returns operations per second in *ops_per_s. */
 int ugb_bench_int_pipe(ugb_ctx* ctx, int kind, double* ops_per_s);
 
+/* ---- harness tooling: synthetic circuits with a VALID trusted setup ----
+ * The reference has no setup tool (zkeys come from snarkjs); benchmarks at 2^20..2^24 constraints need
+ * keys whose proofs verify, and the ~5n fixed-base scalar multiplications of a setup need the GPU.
+ * ultra == 0: Groth16 chain circuit with domainSize 2^logn (zkey protocol 1, wtns v2);
+ * ultra != 0: UltraGroth chain + range-lookup circuit (protocol 1337, .uwtns sections 3..6), table size
+ * 2^lookup_bits, n_chunks looked-up signals.  Buffers are malloc'ed here; release with ugb_host_free. */
+int ugb_synth_build(ugb_ctx* ctx, int ultra, int logn, uint64_t seed, int lookup_bits, uint32_t n_chunks, void** zkey, uint64_t* zkey_size,
+                    void** wtns, uint64_t* wtns_size, char** vk_json);
+void ugb_host_free(void* p);
+/* h_out[i] = h_scalars[i] * G (group 1: G1 generator (1,2), 64-byte affine; group 2: G2 generator, 128 bytes);
+ * scalars are raw 32-byte little-endian integers on the host */
+int ugb_fixed_base_mul(ugb_ctx* ctx, int group, const void* h_scalars, uint64_t n, void* h_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -254,3 +254,13 @@ def vk_from_snarkjs_json(text):
     g2 = lambda v: ((int(v[0][0]), int(v[0][1])), (int(v[1][0]), int(v[1][1])))
     return dict(alpha1=g1(d['vk_alpha_1']), beta2=g2(d['vk_beta_2']), gamma2=g2(d['vk_gamma_2']),
                 delta2=g2(d['vk_delta_2']), IC=[g1(p) for p in d['IC']])
+
+
+def vk_from_ultragroth_json(text):
+    """UltraGroth verification key field names (src/ultra_groth.cpp:542-563)."""
+    d = json.loads(text)
+    g1 = lambda v: None if int(v[2]) == 0 else (int(v[0]), int(v[1]))
+    g2 = lambda v: ((int(v[0][0]), int(v[0][1])), (int(v[1][0]), int(v[1][1])))
+    return dict(alpha1=g1(d['vk_alpha_1']), beta2=g2(d['vk_beta_2']), gamma2=g2(d['vk_gamma_2']),
+                final_delta2=g2(d['vk_delta_c2_2']), round_delta2=g2(d['vk_delta_c1_2']),
+                IC=[g1(p) for p in d['IC']], IC_rand=g1(d['IC_rand']))

@@ -53,6 +53,10 @@ def _declare(L):
     L.ugb_ntt.argtypes = [vp, vp, i32, i32]
     L.ugb_coset_transform.argtypes = [vp, c.POINTER(vp), i32, i32]
     L.ugb_bench_int_pipe.argtypes = [vp, i32, c.POINTER(c.c_double)]
+    L.ugb_synth_build.argtypes = [vp, i32, i32, u64, i32, c.c_uint32, c.POINTER(vp), c.POINTER(u64), c.POINTER(vp), c.POINTER(u64), c.POINTER(vp)]
+    L.ugb_host_free.argtypes = [vp]
+    L.ugb_host_free.restype = None
+    L.ugb_fixed_base_mul.argtypes = [vp, i32, vp, u64, vp]
     # prover extensions
     L.ugb_prover_set_blinding.argtypes = [vp, vp, vp, vp]
     L.ugb_prover_last_h.argtypes = [vp, vp, u64]

@@ -9,7 +9,14 @@
 #include "msm.hpp"
 #include "ntt.hpp"
 
-namespace ug { double bench_int_pipe(DeviceCtx& ctx, int kind); }
+#include <cstdlib>
+#include <vector>
+namespace ug {
+double bench_int_pipe(DeviceCtx& ctx, int kind);
+void synth_build(DeviceCtx& ctx, int ultra, int logn, uint64_t seed, int lookup_bits, uint32_t n_chunks, std::vector<uint8_t>& zkey,
+                 std::vector<uint8_t>& wtns, std::string& vk_json);
+void fixed_base_mul_host(DeviceCtx& ctx, int group, const void* scalars_raw, uint64_t n, void* out);
+}
 
 using namespace ug;
 
@@ -155,6 +162,31 @@ int ugb_coset_transform(ugb_ctx* ctx, void* const* d_vecs, int count, int logn) 
 int ugb_bench_int_pipe(ugb_ctx* ctx, int kind, double* ops_per_s) {
     UGB_TRY
     *ops_per_s = bench_int_pipe(ctx->dev, kind);
+    UGB_CATCH
+}
+
+int ugb_synth_build(ugb_ctx* ctx, int ultra, int logn, uint64_t seed, int lookup_bits, uint32_t n_chunks, void** zkey, uint64_t* zkey_size,
+                    void** wtns, uint64_t* wtns_size, char** vk_json) {
+    UGB_TRY
+    std::vector<uint8_t> zk, wt;
+    std::string vk;
+    synth_build(ctx->dev, ultra, logn, seed, lookup_bits, n_chunks, zk, wt, vk);
+    *zkey = malloc(zk.size());
+    *wtns = malloc(wt.size());
+    *vk_json = (char*)malloc(vk.size() + 1);
+    if (!*zkey || !*wtns || !*vk_json) throw std::bad_alloc();
+    memcpy(*zkey, zk.data(), zk.size());
+    memcpy(*wtns, wt.data(), wt.size());
+    memcpy(*vk_json, vk.c_str(), vk.size() + 1);
+    *zkey_size = zk.size();
+    *wtns_size = wt.size();
+    UGB_CATCH
+}
+void ugb_host_free(void* p) { free(p); }
+int ugb_fixed_base_mul(ugb_ctx* ctx, int group, const void* h_scalars, uint64_t n, void* h_out) {
+    UGB_TRY
+    if (group != 1 && group != 2) throw std::invalid_argument("group must be 1 or 2");
+    fixed_base_mul_host(ctx->dev, group, h_scalars, n, h_out);
     UGB_CATCH
 }
 

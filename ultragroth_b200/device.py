@@ -106,3 +106,27 @@ class Context:
         v = ctypes.c_double()
         check(lib().ugb_bench_int_pipe(self.handle, kind, ctypes.byref(v)))
         return v.value
+
+    def synth(self, logn, seed=0xB200, ultra=False, lookup_bits=4, n_chunks=8):
+        """Synthetic circuit + valid trusted setup -> (zkey bytes, wtns bytes, vk json str)."""
+        zk, wt, vk = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p()
+        zn, wn = ctypes.c_uint64(), ctypes.c_uint64()
+        check(lib().ugb_synth_build(self.handle, 1 if ultra else 0, logn, seed, lookup_bits, n_chunks, ctypes.byref(zk), ctypes.byref(zn),
+                                    ctypes.byref(wt), ctypes.byref(wn), ctypes.byref(vk)))
+        try:
+            zkey = np.ctypeslib.as_array(ctypes.cast(zk, ctypes.POINTER(ctypes.c_uint8)), shape=(zn.value,)).copy()
+            wtns = np.ctypeslib.as_array(ctypes.cast(wt, ctypes.POINTER(ctypes.c_uint8)), shape=(wn.value,)).copy()
+            vkj = ctypes.string_at(vk).decode()
+        finally:
+            lib().ugb_host_free(zk)
+            lib().ugb_host_free(wt)
+            lib().ugb_host_free(vk)
+        return zkey, wtns, vkj
+
+    def fixed_base_mul(self, group, scalars):
+        """[k * G for k in scalars] as zkey-layout bytes."""
+        n = len(scalars)
+        src = b"".join(int(k).to_bytes(32, "little") for k in scalars)
+        out = ctypes.create_string_buffer((64 if group == 1 else 128) * max(n, 1))
+        check(lib().ugb_fixed_base_mul(self.handle, group, src, n, out))
+        return out.raw[:(64 if group == 1 else 128) * n]
