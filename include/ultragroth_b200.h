@@ -96,6 +96,12 @@ int ugb_prover_last_h(void* prover_object, void* h_out, uint64_t bytes);
 int ugb_prover_set_timing(void* prover_object, int enable);
 int ugb_prover_last_times(void* prover_object, float* out, int count);
 uint64_t ugb_prover_kernel_launches(void* prover_object);
+/* re-runs the device part of a proof (MSMs + H pipeline) on the witness left in HBM by the previous
+ * *_prover_prove call: no host->device input copy (bench.py's device-resident leg) */
+int ugb_prover_prove_resident(void* prover_object);
+/* per-kernel device time from CUDA events on the launching stream; stats text is "name\tlaunches\tms\n" */
+int ugb_prover_set_profile(void* prover_object, int enable);
+uint64_t ugb_prover_kernel_stats(void* prover_object, char* out, uint64_t cap);
 void* ugb_prover_stream(void* prover_object);
 
 /* ---- microbenchmarks for the roofline denominators ----

@@ -1,0 +1,89 @@
+"""CPU tests of the boundary: the C-ABI library loads, exports every symbol include/*.h declares, mirrors the
+reference's validation order and messages for everything that happens before a device is touched, and fails
+loudly (no CPU fallback) when there is no GPU."""
+import ctypes
+import os
+import re
+
+import pytest
+
+import ultragroth_b200 as ug
+from ultragroth_b200 import prover as up
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden", "ref_testdata")
+
+
+def _declared(header):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b((?:ugb|groth16|ultra_groth)_\w+)\s*\(", text)))
+
+
+@pytest.mark.parametrize("header", ["ultragroth_b200.h", "prover.h"])
+def test_library_exports_every_declared_symbol(header):
+    L = ug.lib()
+    names = _declared(header)
+    assert len(names) >= (16 if header == "prover.h" else 20)
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/{header} but not exported"
+
+
+def test_prover_h_has_the_references_16_entry_points():
+    want = []
+    for pre in ("groth16", "ultra_groth"):
+        want += [pre + s for s in ("_public_size_for_zkey_buf", "_public_size_for_zkey_file", "_proof_size", "_prover_create",
+                                   "_prover_create_zkey_file", "_prover_prove", "_prover_destroy", "_prover", "_prover_zkey_file")]
+    assert sorted(want) == _declared("prover.h")
+
+
+def test_sizes_and_header_parsing_without_gpu():
+    zk = open(os.path.join(GOLD, "circuit_final.zkey"), "rb").read()
+    assert up.proof_size("groth16") == 810 and up.proof_size("ultragroth") == 1400
+    assert up.public_size_for_zkey_buf(zk) == 86
+    v = ctypes.c_ulonglong()
+    e = ctypes.create_string_buffer(256)
+    rc = ug.lib().groth16_public_size_for_zkey_file(os.path.join(GOLD, "circuit_final.zkey").encode(), ctypes.byref(v), e, 255)
+    assert rc == 0 and v.value == 86
+    with pytest.raises(up.ProverError) as ei:
+        up.public_size_for_zkey_buf(zk, "ultragroth")
+    assert ei.value.code == up.PROVER_ERROR and ei.value.msg == "zkey file is not ultragroth"
+    with pytest.raises(up.ProverError) as ei:
+        up.public_size_for_zkey_buf(b"wtns" + zk[4:])
+    assert ei.value.msg == "Invalid file type. It should be zkey and it is wtns"
+    with pytest.raises(up.ProverError) as ei:
+        up.public_size_for_zkey_buf(zk[:4] + (2).to_bytes(4, "little") + zk[8:])
+    assert ei.value.msg == "Invalid version. It should be <=1 and it is 2"
+    with pytest.raises(up.ProverError) as ei:
+        up.public_size_for_zkey_buf(zk[:8])
+    assert ei.value.msg == "File is too short."
+    with pytest.raises(up.ProverError) as ei:
+        up.public_size_for_zkey_buf(zk[:1000])
+    assert "is invalid" in ei.value.msg
+
+
+def test_null_arguments_follow_the_reference_order():
+    L = ug.lib()
+    e = ctypes.create_string_buffer(256)
+    assert L.groth16_prover_create(None, b"x", 1, e, 255) == up.PROVER_ERROR and e.value == b"Null prover object"
+    h = ctypes.c_void_p()
+    assert L.groth16_prover_create(ctypes.byref(h), None, 0, e, 255) == up.PROVER_ERROR and e.value == b"Null zkey buffer"
+    n = ctypes.c_ulonglong(0)
+    assert L.groth16_prover_prove(None, b"x", 1, e, ctypes.byref(n), e, ctypes.byref(n), e, 255) == up.PROVER_ERROR
+    assert e.value == b"Null prover object"
+    L.groth16_prover_destroy(None)      # NULL-safe like src/prover.cpp:661-679
+    L.ultra_groth_prover_destroy(None)
+    # error_msg may be NULL
+    assert L.groth16_prover_create(None, b"x", 1, None, 0) == up.PROVER_ERROR
+
+
+def test_no_gpu_means_loud_failure_not_a_cpu_fallback():
+    if ug.lib().ugb_device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(ug.UltraGrothError) as ei:
+        ug.Context(0)
+    assert "no CPU fallback" in str(ei.value)
+    zk = open(os.path.join(GOLD, "circuit_final.zkey"), "rb").read()
+    with pytest.raises(up.ProverError) as ei:
+        up.Prover(zk)
+    assert ei.value.code == up.PROVER_ERROR and "no CPU fallback" in ei.value.msg

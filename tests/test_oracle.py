@@ -1,0 +1,220 @@
+"""CPU tests (no GPU): the oracle is pinned against everything the reference offers for this path.
+
+  * golden vectors produced by the reference's OWN field code and keccak (tests/golden/field_vectors.json,
+    made by tests/golden/make_field_vectors.py from build/f{r,q}_raw_generic.cpp + src/keccak256.cpp)
+  * the reference's only fixture, testdata/ (committed under tests/golden/ref_testdata): header points decode
+    to verification_key.json; prove -> verify -> tampered public input must fail (the reference's CI job,
+    .github/workflows/build.yml:69-81)
+  * the C++ restatement (oracle/cpu_prover.cpp, also the timed CPU baseline) against the Python big-int oracle
+  * the device limb algorithms (ff.cuh / curve.cuh) compiled for the host with a software carry flag
+"""
+import ctypes
+import json
+import os
+import random
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import bn254 as bn
+from oracle import cpu_prover as cp
+from oracle import groth16 as og
+from oracle.formats import ZKey, Wtns
+from tests.util import (chain_points, fe_list_bytes, g1_bytes, g1_from_bytes, g2_bytes, g2_from_bytes, scalars_uniform,
+                        scalars_witness_like)
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+OPS = ["mul", "add", "sub", "neg", "to_mont", "from_mont"]
+
+
+@pytest.fixture(scope="module")
+def vectors():
+    return json.load(open(os.path.join(GOLD, "field_vectors.json")))
+
+
+@pytest.fixture(scope="module")
+def testdata():
+    zk = open(os.path.join(GOLD, "ref_testdata", "circuit_final.zkey"), "rb").read()
+    wt = open(os.path.join(GOLD, "ref_testdata", "witness.wtns"), "rb").read()
+    vk = og.vk_from_snarkjs_json(open(os.path.join(GOLD, "ref_testdata", "verification_key.json")).read())
+    return zk, wt, vk
+
+
+@pytest.fixture(scope="module")
+def emul():
+    """Host build of the DEVICE limb algorithms (tests/emul/emul.cpp includes ultragroth_b200/csrc/curve.cuh)."""
+    out = os.path.join(HERE, "emul", "_build")
+    os.makedirs(out, exist_ok=True)
+    lib = os.path.join(out, "libemul.so")
+    src = os.path.join(HERE, "emul", "emul.cpp")
+    deps = [src] + [os.path.join(HERE, "..", "ultragroth_b200", "csrc", f) for f in ("ff.cuh", "curve.cuh")]
+    if not os.path.exists(lib) or any(os.path.getmtime(lib) < os.path.getmtime(d) for d in deps):
+        subprocess.check_call(["g++", "-O1", "-std=c++17", "-fPIC", "-shared", "-o", lib, src])
+    L = ctypes.CDLL(lib)
+    L.emul_field_op.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long]
+    L.emul_point_op.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    return L
+
+
+def _ints(hexes):
+    return [int(h, 16) for h in hexes]
+
+
+def test_python_oracle_matches_reference_field_code(vectors):
+    for name, mod in (("fr", bn.R), ("fq", bn.Q)):
+        rec = vectors["fields"][name]
+        xs, ys = _ints(rec["x"]), _ints(rec["y"])
+        fns = {"mul": lambda x, y: bn.mont_mul(x, y, mod), "add": lambda x, y: bn.raw_add(x, y, mod),
+               "sub": lambda x, y: bn.raw_sub(x, y, mod), "neg": lambda x, y: bn.raw_neg(x, mod),
+               "to_mont": lambda x, y: bn.to_mont(x, mod), "from_mont": lambda x, y: bn.from_mont(x, mod)}
+        for op in OPS:
+            assert _ints(rec[op]) == [fns[op](x, y) for x, y in zip(xs, ys)], (name, op)
+        assert _ints(rec["unreduced_mul"]) == [bn.mont_mul(x, y, mod) for x, y in zip(_ints(rec["unreduced_x"]), _ints(rec["unreduced_y"]))]
+
+
+def test_cpp_oracle_and_device_limbs_match_reference_field_code(vectors, emul):
+    for fid, (name, mod) in enumerate((("fr", bn.R), ("fq", bn.Q))):
+        rec = vectors["fields"][name]
+        for xs, ys, want in ((_ints(rec["x"]), _ints(rec["y"]), _ints(rec["mul"])),
+                             (_ints(rec["unreduced_x"]), _ints(rec["unreduced_y"]), _ints(rec["unreduced_mul"]))):
+            a, b = fe_list_bytes(xs), fe_list_bytes(ys)
+            got = cp.field_mul(fid, a, b)
+            assert [int.from_bytes(got[i:i + 32], "little") for i in range(0, len(got), 32)] == want
+        xs, ys = _ints(rec["x"]), _ints(rec["y"])
+        a, b = fe_list_bytes(xs), fe_list_bytes(ys)
+        for op, opname in enumerate(OPS):
+            out = ctypes.create_string_buffer(len(a))
+            assert emul.emul_field_op(fid, op, a, b, out, len(xs)) == 0
+            assert [int.from_bytes(out.raw[i:i + 32], "little") for i in range(0, len(a), 32)] == _ints(rec[opname]), (name, opname)
+        # inversion (device fp_inv) against pow
+        nz = [x for x in xs if x % mod][:20]
+        out = ctypes.create_string_buffer(32 * len(nz))
+        mont = [x * bn.MONT_R % mod for x in nz]
+        emul.emul_field_op(fid, 7, fe_list_bytes(mont), fe_list_bytes(mont), out, len(nz))
+        assert [int.from_bytes(out.raw[i:i + 32], "little") for i in range(0, 32 * len(nz), 32)] == [pow(x, -1, mod) * bn.MONT_R % mod for x in nz]
+
+
+def test_keccak_matches_reference(vectors):
+    for k in vectors["keccak256"]:
+        msg = bytes.fromhex(k["msg"])
+        assert bn.keccak256(msg).hex() == k["digest"]
+        assert cp.keccak256(msg).hex() == k["digest"]
+
+
+def _xyzz_bytes(P, group):
+    """affine oracle point -> XYZZ bytes (ZZ = ZZZ = 1) in the device layout"""
+    one = bn.MONT_R % bn.Q
+    if group == 1:
+        if P is None:
+            return b"\0" * 128
+        return g1_bytes(P) + one.to_bytes(32, "little") * 2
+    if P is None:
+        return b"\0" * 256
+    return g2_bytes(P) + (one.to_bytes(32, "little") + b"\0" * 32) * 2
+
+
+def _xyzz_to_affine(b, group):
+    F = bn.G1.F if group == 1 else bn.G2.F
+    n = 32 if group == 1 else 64
+    rd = (lambda s: int.from_bytes(s, "little") * bn.FQ_RINV % bn.Q) if group == 1 else \
+        (lambda s: (int.from_bytes(s[:32], "little") * bn.FQ_RINV % bn.Q, int.from_bytes(s[32:], "little") * bn.FQ_RINV % bn.Q))
+    X, Y, ZZ, ZZZ = (rd(b[i * n:(i + 1) * n]) for i in range(4))
+    if F.is_zero(ZZ):
+        return None
+    return (F.mul(X, F.inv(ZZ)), F.mul(Y, F.inv(ZZZ)))
+
+
+@pytest.mark.parametrize("group", [1, 2])
+def test_device_curve_formulas_on_host(emul, group):
+    """madd / add / dbl / to_affine of curve.cuh, including the doubling, cancellation and infinity branches."""
+    C, gen = (bn.G1, bn.G1_GEN) if group == 1 else (bn.G2, bn.G2_GEN)
+    enc = g1_bytes if group == 1 else g2_bytes
+    dec = g1_from_bytes if group == 1 else g2_from_bytes
+    sz = 128 if group == 1 else 256
+    P, Q2 = C.mul_affine(gen, 5), C.mul_affine(gen, 11)
+    negP = (P[0], C.F.neg(P[1]))
+
+    def run(op, acc, q, neg=0):
+        out = ctypes.create_string_buffer(sz)
+        emul.emul_point_op(group, op, acc, q, neg, out)
+        return out.raw
+
+    accP = _xyzz_bytes(P, group)
+    assert _xyzz_to_affine(run(0, accP, enc(Q2)), group) == C.mul_affine(gen, 16)
+    assert _xyzz_to_affine(run(0, accP, enc(Q2), 1), group) == C.to_affine(C.add(C.to_jac(P), C.neg(C.to_jac(Q2))))
+    assert _xyzz_to_affine(run(0, accP, enc(P)), group) == C.mul_affine(gen, 10)       # P + P -> doubling branch
+    assert _xyzz_to_affine(run(0, accP, enc(negP)), group) is None                     # P - P -> infinity
+    assert _xyzz_to_affine(run(0, accP, enc(None)), group) == P                        # + infinity
+    assert _xyzz_to_affine(run(0, _xyzz_bytes(None, group), enc(Q2)), group) == Q2     # infinity + Q
+    s16 = run(0, accP, enc(Q2))
+    assert _xyzz_to_affine(run(1, s16, accP), group) == C.mul_affine(gen, 21)          # general add
+    assert _xyzz_to_affine(run(1, s16, s16), group) == C.mul_affine(gen, 32)           # add -> doubling
+    assert _xyzz_to_affine(run(2, s16, s16), group) == C.mul_affine(gen, 32)           # dbl
+    aff = ctypes.create_string_buffer(sz // 2)
+    emul.emul_point_op(group, 3, s16, s16, 0, aff)
+    assert dec(aff.raw) == C.mul_affine(gen, 16)
+
+
+def test_testdata_header_matches_verification_key(testdata):
+    zk_bytes, wt_bytes, vk = testdata
+    zk = ZKey(zk_bytes)
+    assert (zk.protocol, zk.nVars, zk.nPublic, zk.domainSize) == (1, 1003, 1, 1024)
+    assert zk.alpha1 == vk["alpha1"] and zk.beta2 == vk["beta2"] and zk.delta2 == vk["delta2"]
+    assert zk.ic() == vk["IC"]
+    wt = Wtns(wt_bytes)
+    assert wt.nVars == 1003 and wt.prime == bn.R and wt.signals()[0] == 1
+
+
+def test_reference_ci_flow_prove_verify_tamper(testdata):
+    """.github/workflows/build.yml:69-81 on the oracle: prove, verify, decrement public[0] -> must fail."""
+    zk, wt, vk = testdata
+    proof, public = og.groth16_prove(zk, wt, 0xabcdef0123456789, 0x123456789abcdef)
+    assert og.groth16_verify(vk, proof, public)
+    assert not og.groth16_verify(vk, proof, [(public[0] - 1) % bn.R])
+    js = og.proof_to_json(proof)
+    assert og.proof_from_json(js)["pi_a"] == proof["pi_a"] and len(js) < 810
+
+
+def test_cpp_oracle_matches_python_oracle_on_testdata(testdata):
+    zk, wt, vk = testdata
+    r, s = 31337, (1 << 247) + 5
+    proof, public, inter = og.groth16_prove(zk, wt, r, s, want_intermediates=True)
+    res = cp.prove(zk, wt, r, s, want_h=True, domain_size=1024, threads=2)
+    p = res["points"]
+    assert g1_from_bytes(p[0:64]) == proof["pi_a"]
+    assert g2_from_bytes(p[64:192]) == proof["pi_b"]
+    assert g1_from_bytes(p[192:256]) == proof["pi_c"]
+    assert [int.from_bytes(res["h"][i:i + 32], "little") for i in range(0, 32 * 1024, 32)] == inter["h"]
+
+
+@pytest.mark.parametrize("group", [1, 2])
+def test_cpp_msm_vs_python(group):
+    C, gen = (bn.G1, bn.G1_GEN) if group == 1 else (bn.G2, bn.G2_GEN)
+    enc = g1_bytes if group == 1 else g2_bytes
+    dec = g1_from_bytes if group == 1 else g2_from_bytes
+    for n, sc_fn in ((1, scalars_uniform), (50, scalars_uniform), (1500, scalars_witness_like)):
+        pts = chain_points(C, gen, n, seed=n)
+        pts[n // 2] = None if n > 1 else pts[0]
+        sc = sc_fn(n, seed=n + 1)
+        got = dec(cp.msm(group, b"".join(enc(P) for P in pts), fe_list_bytes(sc), n, threads=2))
+        assert got == C.to_affine(C.msm(pts, sc))
+
+
+@pytest.mark.parametrize("logn", [0, 1, 3, 8, 11])
+def test_cpp_ntt_vs_python(logn):
+    n = 1 << logn
+    rng = random.Random(logn)
+    xs = [rng.randrange(bn.R) for _ in range(n)]
+    mont = fe_list_bytes([x * bn.MONT_R % bn.R for x in xs])
+    un = lambda b: [int.from_bytes(b[i:i + 32], "little") * bn.FR_RINV % bn.R for i in range(0, len(b), 32)]
+    assert un(cp.ntt(mont, logn, threads=2)) == bn.ntt(xs)
+    assert un(cp.ntt(mont, logn, inverse=True, threads=2)) == bn.ntt(xs, inverse=True)
+
+
+def test_ntt_root_convention():
+    """omega_{2^28} = 5^((r-1)/2^28) (ffiasm / snarkjs convention); a wrong root makes the testdata proof fail."""
+    w = bn.fr_root(28)
+    assert pow(w, 1 << 28, bn.R) == 1 and pow(w, 1 << 27, bn.R) == bn.R - 1
+    assert bn.fr_root(3) == pow(w, 1 << 25, bn.R)

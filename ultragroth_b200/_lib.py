@@ -64,6 +64,10 @@ def _declare(L):
     L.ugb_prover_last_times.argtypes = [vp, c.POINTER(c.c_float), i32]
     L.ugb_prover_kernel_launches.argtypes = [vp]
     L.ugb_prover_kernel_launches.restype = u64
+    L.ugb_prover_prove_resident.argtypes = [vp]
+    L.ugb_prover_set_profile.argtypes = [vp, i32]
+    L.ugb_prover_kernel_stats.argtypes = [vp, vp, u64]
+    L.ugb_prover_kernel_stats.restype = u64
     L.ugb_prover_stream.argtypes = [vp]
     L.ugb_prover_stream.restype = vp
     # the reference's prover C API (include/prover.h)

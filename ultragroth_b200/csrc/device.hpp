@@ -31,6 +31,11 @@ public:
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     uint64_t kernel_launches = 0;  // counted by the launch wrappers (bench.py reports it)
+    // per-kernel device time, measured with CUDA events on the launching stream when `profile` is on
+    bool profile = false;
+    struct KernelStat { double ms = 0; uint64_t launches = 0; };
+    std::map<std::string, KernelStat> kernel_stats;
+    std::map<std::string, uint64_t> counters;  // work counters collected in profile mode (e.g. MSM digit entries)
 
     explicit DeviceCtx(int dev) : device(dev) {
         int count = 0;
@@ -56,6 +61,8 @@ public:
         for (auto& kv : ws_) cudaFree(kv.second.ptr);
         for (auto& kv : pinned_) cudaFreeHost(kv.second.ptr);
         for (auto& kv : events_) cudaEventDestroy(kv.second);
+        for (auto& p : pending_) { cudaEventDestroy(p.e0); cudaEventDestroy(p.e1); }
+        for (auto& e : free_events_) cudaEventDestroy(e);
         if (stream) cudaStreamDestroy(stream);
     }
     DeviceCtx(const DeviceCtx&) = delete;
@@ -86,6 +93,37 @@ public:
         return b.ptr;
     }
     void sync() { activate(); UG_CUDA_CHECK(cudaStreamSynchronize(stream)); }
+    // kernel profiling: prof_begin / prof_end bracket one launch; prof_collect folds finished pairs into kernel_stats
+    void prof_begin(const char* name) {
+        if (!profile) return;
+        Pending p;
+        p.name = name;
+        p.e0 = get_event();
+        p.e1 = get_event();
+        UG_CUDA_CHECK(cudaEventRecord(p.e0, stream));
+        pending_.push_back(p);
+    }
+    void prof_end() {
+        if (!profile || pending_.empty()) return;
+        UG_CUDA_CHECK(cudaEventRecord(pending_.back().e1, stream));
+    }
+    void prof_collect() {
+        if (pending_.empty()) return;
+        UG_CUDA_CHECK(cudaStreamSynchronize(stream));
+        for (auto& p : pending_) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, p.e0, p.e1) == cudaSuccess) {
+                KernelStat& st = kernel_stats[p.name];
+                st.ms += ms;
+                st.launches++;
+            } else {
+                cudaGetLastError();
+            }
+            free_events_.push_back(p.e0);
+            free_events_.push_back(p.e1);
+        }
+        pending_.clear();
+    }
     // named event recorded on the stream / waited on by the host
     void record(const std::string& name) {
         cudaEvent_t& ev = events_[name];
@@ -99,6 +137,15 @@ public:
     }
 
 private:
+    struct Pending { const char* name; cudaEvent_t e0, e1; };
+    std::vector<Pending> pending_;
+    std::vector<cudaEvent_t> free_events_;
+    cudaEvent_t get_event() {
+        if (!free_events_.empty()) { cudaEvent_t e = free_events_.back(); free_events_.pop_back(); return e; }
+        cudaEvent_t e;
+        UG_CUDA_CHECK(cudaEventCreate(&e));
+        return e;
+    }
     std::map<std::string, DeviceBuffer> ws_;
     std::map<std::string, DeviceBuffer> pinned_;
     std::map<std::string, cudaEvent_t> events_;
@@ -108,6 +155,15 @@ private:
     do {                                    \
         (ctx).kernel_launches++;            \
         UG_CUDA_CHECK(cudaGetLastError());  \
+    } while (0)
+
+// UG_KERNEL(ctx, "name", kernel<<<...>>>(...)): counted, error checked and (in profile mode) event timed
+#define UG_KERNEL(ctx, name, ...)   \
+    do {                            \
+        (ctx).prof_begin(name);     \
+        __VA_ARGS__;                \
+        (ctx).prof_end();           \
+        UG_LAUNCH_CHECK(ctx);       \
     } while (0)
 
 }  // namespace ug

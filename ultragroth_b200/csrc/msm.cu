@@ -37,12 +37,9 @@ static void exclusive_scan_u32(DeviceCtx& ctx, const uint32_t* in, uint32_t n, u
                                const std::string& slot) {
     uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     uint32_t* tiles = (uint32_t*)ctx.workspace(slot + ".scan_tiles", (size_t)ntiles * 4);
-    k_scan_tile_sums<<<ntiles, SCAN_BS, 0, ctx.stream>>>(in, n, tiles);
-    UG_LAUNCH_CHECK(ctx);
-    k_scan_tiles<<<1, SCAN_BS, 0, ctx.stream>>>(tiles, ntiles, out_total);
-    UG_LAUNCH_CHECK(ctx);
-    k_scan_apply<<<ntiles, SCAN_BS, 0, ctx.stream>>>(in, n, tiles, out);
-    UG_LAUNCH_CHECK(ctx);
+    UG_KERNEL(ctx, "k_scan_tile_sums", k_scan_tile_sums<<<ntiles, SCAN_BS, 0, ctx.stream>>>(in, n, tiles));
+    UG_KERNEL(ctx, "k_scan_tiles", k_scan_tiles<<<1, SCAN_BS, 0, ctx.stream>>>(tiles, ntiles, out_total));
+    UG_KERNEL(ctx, "k_scan_apply", k_scan_apply<<<ntiles, SCAN_BS, 0, ctx.stream>>>(in, n, tiles, out));
 }
 
 void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d_index, uint64_t n, int force_c,
@@ -60,15 +57,13 @@ void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d
     UG_CUDA_CHECK(cudaMemsetAsync(counts, 0, (size_t)cfg.NB * 4, ctx.stream));
     if (n > 0) {
         int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-        k_digits_count<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, counts);
-        UG_LAUNCH_CHECK(ctx);
+        UG_KERNEL(ctx, "k_digits_count", k_digits_count<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, counts));
     }
     exclusive_scan_u32(ctx, counts, cfg.NB, out.starts, out.starts + cfg.NB, slot);
     UG_CUDA_CHECK(cudaMemcpyAsync(cursor, out.starts, (size_t)cfg.NB * 4, cudaMemcpyDeviceToDevice, ctx.stream));
     if (n > 0) {
         int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-        k_digits_scatter<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, cursor, out.entries);
-        UG_LAUNCH_CHECK(ctx);
+        UG_KERNEL(ctx, "k_digits_scatter", k_digits_scatter<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, cursor, out.entries));
     }
 }
 
@@ -96,16 +91,14 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     uint32_t* keys_b = (uint32_t*)ctx.workspace("msm.pkeys_b", (size_t)K1 * 4);
     P* pts_b = (P*)ctx.workspace("msm.ppts_b", (size_t)K1 * sizeof(P));
 
-    k_accumulate<F><<<blocks, 128, 0, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a);
-    UG_LAUNCH_CHECK(ctx);
+    UG_KERNEL(ctx, (sizeof(F) == 32 ? "k_accumulate<G1>" : "k_accumulate<G2>"), k_accumulate<F><<<blocks, 128, 0, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a));
 
     uint32_t* kin = keys_a; P* pin = pts_a; uint32_t* kout = keys_b; P* pout = pts_b;
     uint32_t Kcur = K;
     while (true) {
         uint32_t g = (Kcur + SEG_BS - 1) / SEG_BS;
         int final_pass = (g == 1);
-        k_seg_reduce<F><<<g, SEG_BS, 0, ctx.stream>>>(kin, pin, Kcur, cfg.NB, buckets, kout, pout, final_pass);
-        UG_LAUNCH_CHECK(ctx);
+        UG_KERNEL(ctx, (sizeof(F) == 32 ? "k_seg_reduce<G1>" : "k_seg_reduce<G2>"), k_seg_reduce<F><<<g, SEG_BS, 0, ctx.stream>>>(kin, pin, Kcur, cfg.NB, buckets, kout, pout, final_pass));
         if (final_pass) break;
         Kcur = 2 * g;
         std::swap(kin, kout);
@@ -118,12 +111,13 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     P* slices = (P*)ctx.workspace("msm.slices", (size_t)nbits * S * sizeof(P));
     P* bits = (P*)ctx.workspace("msm.bits." + slot, (size_t)nbits * sizeof(P));
     dim3 grid(S, cfg.c, cfg.W);
-    k_bucket_bits<F><<<grid, BITS_BS, 0, ctx.stream>>>(buckets, cfg.c, S, slices);
-    UG_LAUNCH_CHECK(ctx);
-    k_sum_slices<F><<<(nbits + 63) / 64, 64, 0, ctx.stream>>>(slices, S, nbits, bits);
-    UG_LAUNCH_CHECK(ctx);
-    void* host = ctx.pinned("msm.bits." + slot, (size_t)nbits * sizeof(P));
+    UG_KERNEL(ctx, (sizeof(F) == 32 ? "k_bucket_bits<G1>" : "k_bucket_bits<G2>"), k_bucket_bits<F><<<grid, BITS_BS, 0, ctx.stream>>>(buckets, cfg.c, S, slices));
+    UG_KERNEL(ctx, (sizeof(F) == 32 ? "k_sum_slices<G1>" : "k_sum_slices<G2>"), k_sum_slices<F><<<(nbits + 63) / 64, 64, 0, ctx.stream>>>(slices, S, nbits, bits));
+    // pinned result slot: nbits partial sums, then the number of digit entries this MSM processed (a counter
+    // for the roofline arithmetic: every entry is one 4-byte index + one affine point gather + one mixed add)
+    uint8_t* host = (uint8_t*)ctx.pinned("msm.bits." + slot, (size_t)nbits * sizeof(P) + 16);
     UG_CUDA_CHECK(cudaMemcpyAsync(host, bits, (size_t)nbits * sizeof(P), cudaMemcpyDeviceToHost, ctx.stream));
+    UG_CUDA_CHECK(cudaMemcpyAsync(host + (size_t)nbits * sizeof(P), dg.starts + cfg.NB, 4, cudaMemcpyDeviceToHost, ctx.stream));
     ctx.record("msm." + slot);
 }
 

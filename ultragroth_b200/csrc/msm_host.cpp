@@ -2,13 +2,18 @@
 // O(W*c) = 255 doublings + additions on the CPU -- the serial tail the reference also runs on the CPU.
 #include "msm.hpp"
 
+#include <cstring>
+
 namespace ug {
 
 template <class HF>
 static void msm_finish_impl(DeviceCtx& ctx, const MsmDigits& dg, const std::string& slot, XYZZ<HF>* out) {
     ctx.wait("msm." + slot);
     int nbits = dg.cfg.W * dg.cfg.c;
-    const XYZZ<HF>* U = (const XYZZ<HF>*)ctx.pinned("msm.bits." + slot, (size_t)nbits * sizeof(XYZZ<HF>));
+    const XYZZ<HF>* U = (const XYZZ<HF>*)ctx.pinned("msm.bits." + slot, (size_t)nbits * sizeof(XYZZ<HF>) + 16);
+    uint32_t entries = 0;
+    memcpy(&entries, (const uint8_t*)U + (size_t)nbits * sizeof(XYZZ<HF>), 4);
+    if (ctx.profile) ctx.counters[sizeof(HF) == 32 ? "#msm_entries<G1>" : "#msm_entries<G2>"] += entries;
     XYZZ<HF> acc = XYZZ<HF>::inf();
     for (int p = nbits - 1; p >= 0; p--) {
         acc = pt_dbl(acc);

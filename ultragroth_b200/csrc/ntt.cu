@@ -83,8 +83,7 @@ void NttTables::fill_powers(Fr* d_out, int logn, const HFr& base, const HFr& fac
     UG_CUDA_CHECK(cudaMemcpyAsync(d_lo, lo.data(), nlo * sizeof(Fr), cudaMemcpyHostToDevice, ctx_.stream));
     UG_CUDA_CHECK(cudaMemcpyAsync(d_hi, hi.data(), (size_t)nhi * sizeof(Fr), cudaMemcpyHostToDevice, ctx_.stream));
     int blocks = (int)std::min<uint64_t>(((uint64_t)n + 255) / 256, (uint64_t)ctx_.sm_count * 8);
-    k_fill_powers<<<blocks, 256, 0, ctx_.stream>>>(d_out, n, logn, d_hi, d_lo, lo_bits, bitrev ? 1 : 0);
-    UG_LAUNCH_CHECK(ctx_);
+    UG_KERNEL(ctx_, "k_fill_powers", k_fill_powers<<<blocks, 256, 0, ctx_.stream>>>(d_out, n, logn, d_hi, d_lo, lo_bits, bitrev ? 1 : 0));
     UG_CUDA_CHECK(cudaStreamSynchronize(ctx_.stream));  // host vectors go out of scope
 }
 
@@ -191,9 +190,10 @@ void ntt_run(DeviceCtx& ctx, NttTables& tabs, Fr* const* d_vecs, int count, int 
         const size_t smem = (size_t)E * 32;
         const int bt = (int)std::min<uint32_t>(threads, std::max<uint32_t>(32, E / 2));
         dim3 grid(tiles, count);
-        if (dif) k_ntt_pass<true><<<grid, bt, smem, ctx.stream>>>(a);
-        else k_ntt_pass<false><<<grid, bt, smem, ctx.stream>>>(a);
-        UG_LAUNCH_CHECK(ctx);
+        const char* kname = dif ? (ps.lo ? "k_ntt_pass<dif,strided>" : "k_ntt_pass<dif,contig>")
+                                : (ps.lo ? "k_ntt_pass<dit,strided>" : "k_ntt_pass<dit,contig>");
+        if (dif) UG_KERNEL(ctx, kname, k_ntt_pass<true><<<grid, bt, smem, ctx.stream>>>(a));
+        else UG_KERNEL(ctx, kname, k_ntt_pass<false><<<grid, bt, smem, ctx.stream>>>(a));
     }
 }
 
@@ -205,8 +205,7 @@ void ntt_natural(DeviceCtx& ctx, NttTables& tabs, Fr* d_vec, int logn, bool inve
     if (logn >= 2) {
         const uint32_t n = 1u << logn;
         int blocks = (int)std::min<uint64_t>(((uint64_t)n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-        k_bitrev_swap<<<blocks, 256, 0, ctx.stream>>>(d_vec, n, logn);
-        UG_LAUNCH_CHECK(ctx);
+        UG_KERNEL(ctx, "k_bitrev_swap", k_bitrev_swap<<<blocks, 256, 0, ctx.stream>>>(d_vec, n, logn));
     }
 }
 

@@ -521,6 +521,31 @@ int ugb_prover_last_times(void* prover_object, float* out, int count) {
     for (int i = 0; i < count && i < (int)(sizeof(v) / sizeof(v[0])); i++) out[i] = v[i];
     return UGB_OK;
 }
+int ugb_prover_prove_resident(void* prover_object) {
+    if (!prover_object) return UGB_ERROR;
+    try {
+        ProofMsms m;
+        static_cast<ProverBase*>(prover_object)->dev->prove_resident(m);
+    } catch (...) { return UGB_ERROR; }
+    return UGB_OK;
+}
+int ugb_prover_set_profile(void* prover_object, int enable) {
+    if (!prover_object) return UGB_ERROR;
+    DeviceCtx& c = static_cast<ProverBase*>(prover_object)->dev->ctx();
+    c.profile = enable != 0;
+    if (enable) { c.kernel_stats.clear(); c.counters.clear(); }
+    return UGB_OK;
+}
+// "name\tlaunches\tms\n" per kernel, NUL terminated; returns the number of bytes needed
+uint64_t ugb_prover_kernel_stats(void* prover_object, char* out, uint64_t cap) {
+    if (!prover_object) return 0;
+    DeviceCtx& c = static_cast<ProverBase*>(prover_object)->dev->ctx();
+    std::string s;
+    for (auto& kv : c.kernel_stats) s += kv.first + "\t" + std::to_string(kv.second.launches) + "\t" + std::to_string(kv.second.ms) + "\n";
+    for (auto& kv : c.counters) s += kv.first + "\t" + std::to_string(kv.second) + "\t0\n";
+    if (out && cap) { strncpy(out, s.c_str(), cap - 1); out[cap - 1] = 0; }
+    return s.size() + 1;
+}
 uint64_t ugb_prover_kernel_launches(void* prover_object) {
     if (!prover_object) return 0;
     return static_cast<ProverBase*>(prover_object)->dev->ctx().kernel_launches;

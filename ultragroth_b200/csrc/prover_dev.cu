@@ -35,6 +35,38 @@ __global__ void __launch_bounds__(256) k_spmv_abc(const uint32_t* __restrict__ r
     }
 }
 
+// Rows with more than SPMV_LONG_ROW terms (UltraGroth's "sum of all lookup terms" constraint has one term per
+// looked-up signal) get a whole CTA each: strided partial sums, shared-memory tree, then c = a*b is refreshed.
+constexpr uint32_t SPMV_LONG_ROW = 48;
+constexpr int SPMV_LONG_BS = 512;
+struct LongRow { uint32_t slot /* m*n + row */, lo, hi; };
+
+__global__ void __launch_bounds__(SPMV_LONG_BS) k_spmv_long(const LongRow* __restrict__ rows, const uint32_t* __restrict__ sig,
+                                                            const Fr* __restrict__ coef, const Fr* __restrict__ w, uint32_t n,
+                                                            Fr* __restrict__ a, Fr* __restrict__ b) {
+    __shared__ Fr sh[SPMV_LONG_BS];
+    const LongRow r = rows[blockIdx.x];
+    Fr acc = Fr::zero();
+    for (uint32_t k = r.lo + threadIdx.x; k < r.hi; k += SPMV_LONG_BS) acc = fp_add(acc, fp_mul(ld_nc(&w[sig[k]]), ld_nc(&coef[k])));
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int d = SPMV_LONG_BS / 2; d > 0; d >>= 1) {
+        if ((int)threadIdx.x < d) sh[threadIdx.x] = fp_add(sh[threadIdx.x], sh[threadIdx.x + d]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        if (r.slot < n) st_g(&a[r.slot], sh[0]);
+        else st_g(&b[r.slot - n], sh[0]);
+    }
+}
+__global__ void k_spmv_fix_c(const LongRow* __restrict__ rows, uint32_t count, uint32_t n, const Fr* __restrict__ a,
+                             const Fr* __restrict__ b, Fr* __restrict__ c) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    uint32_t row = rows[i].slot % n;
+    st_g(&c[row], fp_mul(ld_g(&a[row]), ld_g(&b[row])));
+}
+
 // h[i] = fromMontgomery(a[i]*b[i] - c[i])   (src/groth16.cpp:142-148), written over a
 __global__ void __launch_bounds__(256) k_h_final(Fr* __restrict__ a, const Fr* __restrict__ b, const Fr* __restrict__ c, uint32_t n) {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -197,15 +229,26 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
         const uint8_t* rec = sec + 4;
         nCoefs_ = cnt;
         const uint32_t n = domainSize;
-        std::vector<uint32_t> rp((size_t)2 * n + 1, 0);
+        std::vector<uint32_t> len((size_t)2 * n, 0);
         for (uint64_t k = 0; k < cnt; k++) {
             uint32_t m, c, s;
             memcpy(&m, rec + k * 44, 4); memcpy(&c, rec + k * 44 + 4, 4); memcpy(&s, rec + k * 44 + 8, 4);
             if (m > 1 || c >= n || s >= nVars) throw std::range_error("zkey coefficient record out of range");
-            rp[(size_t)m * n + c + 1]++;
+            len[(size_t)m * n + c]++;
         }
-        for (size_t i = 0; i < (size_t)2 * n; i++) rp[i + 1] += rp[i];
+        // short rows form the CSR proper; long rows keep an empty CSR row and live after `short_total`
+        std::vector<uint32_t> rp((size_t)2 * n + 1, 0);
+        std::vector<LongRow> longs;
+        for (size_t i = 0; i < (size_t)2 * n; i++) rp[i + 1] = rp[i] + (len[i] > SPMV_LONG_ROW ? 0 : len[i]);
+        uint32_t tail = rp[(size_t)2 * n];
         std::vector<uint32_t> cur(rp.begin(), rp.end() - 1);
+        for (size_t i = 0; i < (size_t)2 * n; i++) {
+            if (len[i] > SPMV_LONG_ROW) {
+                longs.push_back(LongRow{(uint32_t)i, tail, tail + len[i]});
+                cur[i] = tail;
+                tail += len[i];
+            }
+        }
         std::vector<uint32_t> sig(cnt);
         std::vector<uint8_t> val(cnt * 32);
         for (uint64_t k = 0; k < cnt; k++) {
@@ -215,6 +258,8 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
             sig[pos] = s;
             memcpy(&val[(size_t)pos * 32], rec + k * 44 + 12, 32);
         }
+        n_long_ = (uint32_t)longs.size();
+        if (n_long_) long_rows_ = upload(ctx, longs.data(), longs.size() * sizeof(LongRow));
         row_ptr_ = (uint32_t*)upload(ctx, rp.data(), rp.size() * 4);
         coef_sig_ = (uint32_t*)upload(ctx, sig.data(), sig.size() * 4);
         coef_val_ = upload(ctx, val.data(), val.size());
@@ -239,7 +284,7 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
 ProverDevice::~ProverDevice() {
     cudaSetDevice(ctx_->device);
     cudaStreamSynchronize(ctx_->stream);
-    for (void* p : {A_, B1_, B2_, C_, H_, C1_, (void*)idx_c1_, (void*)idx_c2_, (void*)row_ptr_, (void*)coef_sig_, coef_val_, w_, a_, b_, c_})
+    for (void* p : {long_rows_, A_, B1_, B2_, C_, H_, C1_, (void*)idx_c1_, (void*)idx_c2_, (void*)row_ptr_, (void*)coef_sig_, coef_val_, w_, a_, b_, c_})
         if (p) cudaFree(p);
     for (auto& e : ev_) cudaEventDestroy(e);
 }
@@ -284,8 +329,11 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     mark();  // 5
     // H pipeline
     int blocks = (int)std::min<uint64_t>(((uint64_t)n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-    k_spmv_abc<<<blocks, 256, 0, ctx.stream>>>(row_ptr_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, n, (Fr*)a_, (Fr*)b_, (Fr*)c_);
-    UG_LAUNCH_CHECK(ctx);
+    UG_KERNEL(ctx, "k_spmv_abc", k_spmv_abc<<<blocks, 256, 0, ctx.stream>>>(row_ptr_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, n, (Fr*)a_, (Fr*)b_, (Fr*)c_));
+    if (n_long_) {
+        UG_KERNEL(ctx, "k_spmv_long", k_spmv_long<<<n_long_, SPMV_LONG_BS, 0, ctx.stream>>>((const LongRow*)long_rows_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, n, (Fr*)a_, (Fr*)b_));
+        UG_KERNEL(ctx, "k_spmv_fix_c", k_spmv_fix_c<<<(n_long_ + 127) / 128, 128, 0, ctx.stream>>>((const LongRow*)long_rows_, n_long_, n, (const Fr*)a_, (const Fr*)b_, (Fr*)c_));
+    }
     mark();  // 6
     Fr* vecs[3] = {(Fr*)a_, (Fr*)b_, (Fr*)c_};
     // ifft + coset shift (+ 1/n) fused, output bit-reversed; then fft from bit-reversed to natural
@@ -293,8 +341,7 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     mark();  // 7
     ntt_run(ctx, *tabs_, vecs, 3, logn, NTT_BITREV_TO_NATURAL, false, nullptr, nullptr);
     mark();  // 8
-    k_h_final<<<blocks, 256, 0, ctx.stream>>>((Fr*)a_, (const Fr*)b_, (const Fr*)c_, n);
-    UG_LAUNCH_CHECK(ctx);
+    UG_KERNEL(ctx, "k_h_final", k_h_final<<<blocks, 256, 0, ctx.stream>>>((Fr*)a_, (const Fr*)b_, (const Fr*)c_, n));
     mark();  // 9
     MsmDigits dh;
     msm_sort_digits(ctx, (const uint8_t*)a_, nullptr, n, 0, "h", dh);
@@ -306,6 +353,7 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     msm_g2_finish(ctx, dw, "b2", &out.b2);
     msm_g1_finish(ctx, c_shares_witness_sort_ ? dw : dc, "c", &out.c);
     msm_g1_finish(ctx, dh, "h", &out.h);
+    ctx.prof_collect();
     if (timing) {
         UG_CUDA_CHECK(cudaEventSynchronize(ev_[11]));
         float* dst[] = {&last_times.sort_w, &last_times.msm_a, &last_times.msm_b1, &last_times.msm_b2, &last_times.msm_c, &last_times.spmv,
@@ -320,6 +368,12 @@ void ProverDevice::prove_groth16(const uint8_t* witness, ProofMsms& out) {
     ctx.activate();
     UG_CUDA_CHECK(cudaMemcpyAsync(w_, witness, (size_t)nVars * 32, cudaMemcpyHostToDevice, ctx.stream));
     h_pipeline_and_msms(out, false);
+}
+
+void ProverDevice::prove_resident(ProofMsms& out) {
+    ctx_->activate();
+    if (ultra_) ultra_round_msm(out.round_c);  // same MSM shape as a real proof's first round
+    h_pipeline_and_msms(out, ultra_);
 }
 
 void ProverDevice::ultra_upload_witness(const uint8_t* witness) {
@@ -366,13 +420,11 @@ void ProverDevice::ultra_lookup(const uint32_t* chunks, uint32_t chunks_len, con
     memcpy(&rr, &raw, 32);
     if (freqs_len) {
         uint32_t threads = (freqs_len + LOOKUP_RUN - 1) / LOOKUP_RUN;
-        k_lookup_inverses<<<(threads + 127) / 128, 128, 0, ctx.stream>>>(d_freqs, freqs_len, rm, d_inv2, d_prod);
-        UG_LAUNCH_CHECK(ctx);
+        UG_KERNEL(ctx, "k_lookup_inverses", k_lookup_inverses<<<(threads + 127) / 128, 128, 0, ctx.stream>>>(d_freqs, freqs_len, rm, d_inv2, d_prod));
     }
     if (idx_len) {
         int blocks = (int)std::min<uint64_t>(((uint64_t)idx_len + 255) / 256, (uint64_t)ctx.sm_count * 8);
-        k_lookup_push<<<blocks, 256, 0, ctx.stream>>>(d_widx, d_pidx, idx_len, d_chunks, chunks_len, freqs_len, rr, d_inv2, d_prod, (Fr*)w_);
-        UG_LAUNCH_CHECK(ctx);
+        UG_KERNEL(ctx, "k_lookup_push", k_lookup_push<<<blocks, 256, 0, ctx.stream>>>(d_widx, d_pidx, idx_len, d_chunks, chunks_len, freqs_len, rr, d_inv2, d_prod, (Fr*)w_));
     }
     UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));  // host index arrays are borrowed
 }

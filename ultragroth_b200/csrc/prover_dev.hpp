@@ -37,6 +37,9 @@ public:
     // ---- Groth16 (src/groth16.cpp:48-203 up to the blinding) ----
     // witness: nVars raw 32-byte scalars on the host
     void prove_groth16(const uint8_t* witness, ProofMsms& out);
+    // the same device work on the witness already resident in HBM from the previous proof (no host copies
+    // in: bench.py's device-resident throughput leg)
+    void prove_resident(ProofMsms& out);
 
     // ---- UltraGroth (src/ultra_groth.cpp:401-462) ----
     void ultra_upload_witness(const uint8_t* witness);
@@ -69,6 +72,8 @@ private:
     uint32_t* coef_sig_ = nullptr;
     void* coef_val_ = nullptr;
     uint64_t nCoefs_ = 0;
+    void* long_rows_ = nullptr;  // rows too long for one thread (see k_spmv_long)
+    uint32_t n_long_ = 0;
     // per-proof buffers
     void *w_ = nullptr, *a_ = nullptr, *b_ = nullptr, *c_ = nullptr;
     std::vector<cudaEvent_t> ev_;

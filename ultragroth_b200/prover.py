@@ -107,6 +107,26 @@ class Prover:
             raise ProverError(rc, "ugb_prover_last_h failed")
         return out.raw
 
+    def prove_resident(self):
+        """Device part of a proof on the witness already in HBM (no host copies in)."""
+        rc = lib().ugb_prover_prove_resident(self.handle)
+        if rc:
+            raise ProverError(rc, "ugb_prover_prove_resident failed")
+
+    def set_profile(self, on=True):
+        lib().ugb_prover_set_profile(self.handle, 1 if on else 0)
+
+    def kernel_stats(self):
+        """{kernel name: (launches, total ms)} from CUDA events on the prover's stream."""
+        n = lib().ugb_prover_kernel_stats(self.handle, None, 0)
+        buf = ctypes.create_string_buffer(int(n) + 16)
+        lib().ugb_prover_kernel_stats(self.handle, buf, len(buf))
+        out = {}
+        for line in buf.value.decode().splitlines():
+            name, cnt, ms = line.split("\t")
+            out[name] = (int(cnt), float(ms))
+        return out
+
     @property
     def kernel_launches(self):
         return int(lib().ugb_prover_kernel_launches(self.handle))
