@@ -39,6 +39,62 @@ __global__ void __launch_bounds__(256) k_bench_imad_wide(uint64_t* out, uint32_t
     if (s == 0x12345678u) out[0] = s;
 }
 
+
+// kind 3: the carry-linked row of the Montgomery product: mad.lo.cc / madc.hi.cc pairs, which ptxas fuses into
+// one IMAD.WIDE.U32 (carry out) followed by IMAD.WIDE.U32.X (carry in + out).  4 wide multiply-adds per row,
+// 4 independent rows per thread.
+__global__ void __launch_bounds__(256) k_bench_imad_wide_x(uint32_t* out, uint32_t seed) {
+    uint32_t a[4][8];
+    uint32_t y[4];
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+#pragma unroll
+        for (int i = 0; i < 8; i++) a[r][i] = seed + threadIdx.x * 8 + i + r;
+#pragma unroll
+    for (int i = 0; i < 4; i++) y[i] = seed * (i + 3) + threadIdx.x;
+    uint32_t x = seed | 1u;
+    for (int it = 0; it < IB_ITERS / 2; it++) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            a[r][0] = mad_lo_cc(y[0], x, a[r][0]);
+            a[r][1] = madc_hi_cc(y[0], x, a[r][1]);
+            a[r][2] = madc_lo_cc(y[1], x, a[r][2]);
+            a[r][3] = madc_hi_cc(y[1], x, a[r][3]);
+            a[r][4] = madc_lo_cc(y[2], x, a[r][4]);
+            a[r][5] = madc_hi_cc(y[2], x, a[r][5]);
+            a[r][6] = madc_lo_cc(y[3], x, a[r][6]);
+            a[r][7] = madc_hi(y[3], x, a[r][7]);
+        }
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+#pragma unroll
+        for (int i = 0; i < 8; i++) s ^= a[r][i];
+    if (s == 0x12345678u) out[0] = s;
+}
+
+// kind 4: carry OUT only: (mad.lo.cc, madc.hi.cc) + addc into a separate word -> IMAD.WIDE.U32 writing a predicate,
+// consumed by an IADD3.X on the ALU pipe.  8 independent accumulators per thread.
+__global__ void __launch_bounds__(256) k_bench_imad_wide_cout(uint32_t* out, uint32_t seed) {
+    uint32_t lo[8], hi[8], c[8], y[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { lo[i] = seed + threadIdx.x + i; hi[i] = seed * 3 + i; c[i] = 0; y[i] = seed * (i + 3) + threadIdx.x; }
+    uint32_t x = seed | 1u;
+    for (int it = 0; it < IB_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            lo[i] = mad_lo_cc(y[i], x, lo[i]);
+            hi[i] = madc_hi_cc(y[i], x, hi[i]);
+            c[i] = addc(c[i], 0);
+        }
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s ^= lo[i] ^ hi[i] ^ c[i];
+    if (s == 0x12345678u) out[0] = s;
+}
+
 constexpr int MB_ITERS = 256;
 __global__ void __launch_bounds__(256) k_bench_modmul(Fq* out, uint32_t seed) {
     Fq a[4];
@@ -69,6 +125,8 @@ double bench_int_pipe(DeviceCtx& ctx, int kind) {
         UG_CUDA_CHECK(cudaEventRecord(e0, ctx.stream));
         if (kind == 0) { k_bench_imad<<<blocks, 256, 0, ctx.stream>>>((uint32_t*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
         else if (kind == 1) { k_bench_imad_wide<<<blocks, 256, 0, ctx.stream>>>((uint64_t*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
+        else if (kind == 3) { k_bench_imad_wide_x<<<blocks, 256, 0, ctx.stream>>>((uint32_t*)d, 7 + rep); ops = (double)blocks * 256 * 16 * (IB_ITERS / 2); }
+        else if (kind == 4) { k_bench_imad_wide_cout<<<blocks, 256, 0, ctx.stream>>>((uint32_t*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
         else { k_bench_modmul<<<blocks, 256, 0, ctx.stream>>>((Fq*)d, 7 + rep); ops = (double)blocks * 256 * 4 * MB_ITERS; }
         UG_LAUNCH_CHECK(ctx);
         UG_CUDA_CHECK(cudaEventRecord(e1, ctx.stream));
