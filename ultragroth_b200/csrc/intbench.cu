@@ -28,10 +28,14 @@ __global__ void __launch_bounds__(256) k_bench_imad_wide(uint64_t* out, uint32_t
     uint32_t x[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) { a[i] = seed + threadIdx.x * 8 + i; x[i] = seed * (i + 3) + threadIdx.x; }
-    uint32_t m = seed | 1u;
     for (int it = 0; it < IB_ITERS; it++) {
 #pragma unroll
-        for (int i = 0; i < 8; i++) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(a[i]) : "r"(x[i]), "r"(m));
+        for (int i = 0; i < 8; i++) {
+            // the multiplier is the low word of a neighbouring accumulator: nothing is loop invariant (a first version
+            // with a constant multiplier was strength-reduced by ptxas to IADD3 pairs and overstated the rate 2x)
+            uint32_t y = (uint32_t)a[(i + 1) & 7];
+            asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(a[i]) : "r"(x[i]), "r"(y));
+        }
     }
     uint64_t s = 0;
 #pragma unroll
@@ -103,10 +107,9 @@ __global__ void __launch_bounds__(256) k_bench_modmul(Fq* out, uint32_t seed) {
         a[i] = Fq::one();
         a[i].v[0] += seed + threadIdx.x + i;
     }
-    Fq m = Fq::rsquared();
     for (int it = 0; it < MB_ITERS; it++) {
 #pragma unroll
-        for (int i = 0; i < 4; i++) a[i] = fp_mul(a[i], m);
+        for (int i = 0; i < 4; i++) a[i] = fp_mul(a[i], a[(i + 1) & 3]);
     }
     Fq s = fp_add(fp_add(a[0], a[1]), fp_add(a[2], a[3]));
     if (s.v[0] == 0x12345678u && s.v[7] == 1) out[0] = s;

@@ -1,4 +1,4 @@
-// MSM driver: launches the kernels of msm.cuh and combines the per-bit sums on the host.
+// MSM driver: launches the kernels of msm.cuh; the host combines the per-level / per-window partial sums (msm_host.cpp).
 #include "msm.cuh"
 #include "msm.hpp"
 
@@ -7,30 +7,54 @@
 
 namespace ug {
 
-MsmConfig msm_pick_config(uint64_t n, int force_c) {
+static int env_int_msm(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+MsmConfig msm_pick_config(uint64_t n, int force_c, bool pre) {
     int best_c = 0;
-    if (force_c <= 0) {
-        const char* env = getenv("UGB_MSM_C");
-        if (env) force_c = atoi(env);
-    }
+    if (force_c <= 0) force_c = env_int_msm(pre ? "UGB_MSM_PRE_C" : "UGB_MSM_C", 0);
     if (force_c > 0) {
-        best_c = std::min(std::max(force_c, 2), 22);
+        best_c = std::min(std::max(force_c, 2), 23);
     } else {
-        // cost in modular multiplications: n*W mixed adds (10) + W*c*(B/2) bucket-bit adds (14)
+        // cost in modular multiplications: n*W mixed additions (10 each) + 2 additions (14 each) per bucket for the
+        // running-sum reduction + bucket memset / histogram traffic (~2 per bucket)
         double best = 1e300;
-        for (int c = 4; c <= 20; c++) {
+        for (int c = 4; c <= (pre ? 22 : 20); c++) {
             double W = (255 + c - 1) / c;
             double B = (double)(1u << (c - 1));
-            double cost = (double)n * W * 10.0 + W * c * (B / 2) * 14.0 + W * B * 2.0 /* bucket memset + scan */;
+            double sets = pre ? 1.0 : W;
+            if ((double)n * W >= 2147483648.0) continue;  // table index + sign bit must fit 32 bits
+            double cost = (double)n * W * 10.0 + sets * B * 30.0;
             if (cost < best) { best = cost; best_c = c; }
         }
+        if (best_c == 0) best_c = 16;
     }
     MsmConfig cfg;
     cfg.c = best_c;
     cfg.W = (255 + best_c - 1) / best_c;
     cfg.B = 1u << (best_c - 1);
-    cfg.NB = (uint32_t)cfg.W * cfg.B;
+    cfg.pre = pre;
+    cfg.NB = pre ? cfg.B : (uint32_t)cfg.W * cfg.B;
     return cfg;
+}
+
+MsmReducePlan msm_reduce_plan(const MsmConfig& cfg) {
+    MsmReducePlan p;
+    // first level: about 64K threads over all windows, chunks of 4..256 buckets
+    uint64_t total = (uint64_t)cfg.B * cfg.nwin();
+    int mu = 2;
+    while (mu < 8 && (total >> mu) > 65536) mu++;
+    p.mu = mu;
+    uint32_t N = cfg.B;
+    while (N > 0) {
+        uint32_t K = (N + (1u << mu) - 1) >> mu;
+        p.N.push_back(N);
+        p.K.push_back(K);
+        N = K - 1;  // next level: chunk sums 1..K-1 with weights 1..K-1
+    }
+    return p;
 }
 
 static void exclusive_scan_u32(DeviceCtx& ctx, const uint32_t* in, uint32_t n, uint32_t* out, uint32_t* out_total,
@@ -43,27 +67,29 @@ static void exclusive_scan_u32(DeviceCtx& ctx, const uint32_t* in, uint32_t n, u
 }
 
 void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d_index, uint64_t n, int force_c,
-                     const std::string& slot, MsmDigits& out) {
+                     const std::string& slot, MsmDigits& out, const MsmConfig* table_cfg) {
     ctx.activate();
     if (n >= (1ull << 31)) throw std::runtime_error("ultragroth_b200: MSM size must be < 2^31");
-    MsmConfig cfg = msm_pick_config(n, force_c);
-    if ((uint64_t)n * cfg.W >= (1ull << 32)) throw std::runtime_error("ultragroth_b200: MSM digit count overflows 32 bits");
+    MsmConfig cfg = table_cfg ? *table_cfg : msm_pick_config(n, force_c, false);
+    if ((uint64_t)n * cfg.W >= (1ull << 31)) throw std::runtime_error("ultragroth_b200: MSM digit count overflows 31 bits");
     out.cfg = cfg;
     out.n = n;
     uint32_t* counts = (uint32_t*)ctx.workspace(slot + ".counts", (size_t)cfg.NB * 4);
     uint32_t* cursor = (uint32_t*)ctx.workspace(slot + ".cursor", (size_t)cfg.NB * 4);
     out.starts = (uint32_t*)ctx.workspace(slot + ".starts", ((size_t)cfg.NB + 1) * 4);
     out.entries = (uint32_t*)ctx.workspace(slot + ".entries", std::max<size_t>((size_t)n * cfg.W * 4, 16));
+    const uint32_t key_stride = cfg.pre ? 0u : cfg.B;
+    const uint32_t entry_stride = cfg.pre ? (uint32_t)n : 0u;
     UG_CUDA_CHECK(cudaMemsetAsync(counts, 0, (size_t)cfg.NB * 4, ctx.stream));
     if (n > 0) {
         int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-        UG_KERNEL(ctx, "k_digits_count", k_digits_count<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, counts));
+        UG_KERNEL(ctx, "k_digits_count", k_digits_count<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, key_stride, counts));
     }
     exclusive_scan_u32(ctx, counts, cfg.NB, out.starts, out.starts + cfg.NB, slot);
     UG_CUDA_CHECK(cudaMemcpyAsync(cursor, out.starts, (size_t)cfg.NB * 4, cudaMemcpyDeviceToDevice, ctx.stream));
     if (n > 0) {
         int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-        UG_KERNEL(ctx, "k_digits_scatter", k_digits_scatter<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, cursor, out.entries));
+        UG_KERNEL(ctx, "k_digits_scatter", k_digits_scatter<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, key_stride, entry_stride, cursor, out.entries));
     }
 }
 
@@ -71,6 +97,7 @@ template <class F>
 static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmDigits& dg, const std::string& slot) {
     ctx.activate();
     const MsmConfig& cfg = dg.cfg;
+    const bool g1 = sizeof(F) == 32;
     using P = XYZZ<F>;
     P* buckets = (P*)ctx.workspace("msm.buckets", (size_t)cfg.NB * sizeof(P));
     UG_CUDA_CHECK(cudaMemsetAsync(buckets, 0, (size_t)cfg.NB * sizeof(P), ctx.stream));
@@ -91,33 +118,52 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     uint32_t* keys_b = (uint32_t*)ctx.workspace("msm.pkeys_b", (size_t)K1 * 4);
     P* pts_b = (P*)ctx.workspace("msm.ppts_b", (size_t)K1 * sizeof(P));
 
-    UG_KERNEL(ctx, (sizeof(F) == 32 ? "k_accumulate<G1>" : "k_accumulate<G2>"), k_accumulate<F><<<blocks, 128, 0, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a));
+    UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), k_accumulate<F><<<blocks, 128, 0, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a));
 
     uint32_t* kin = keys_a; P* pin = pts_a; uint32_t* kout = keys_b; P* pout = pts_b;
     uint32_t Kcur = K;
     while (true) {
         uint32_t g = (Kcur + SEG_BS - 1) / SEG_BS;
         int final_pass = (g == 1);
-        UG_KERNEL(ctx, (sizeof(F) == 32 ? "k_seg_reduce<G1>" : "k_seg_reduce<G2>"), k_seg_reduce<F><<<g, SEG_BS, 0, ctx.stream>>>(kin, pin, Kcur, cfg.NB, buckets, kout, pout, final_pass));
+        UG_KERNEL(ctx, (g1 ? "k_seg_reduce<G1>" : "k_seg_reduce<G2>"), k_seg_reduce<F><<<g, SEG_BS, 0, ctx.stream>>>(kin, pin, Kcur, cfg.NB, buckets, kout, pout, final_pass));
         if (final_pass) break;
         Kcur = 2 * g;
         std::swap(kin, kout);
         std::swap(pin, pout);
     }
 
-    // bucket reduction to per-bit sums
-    int S = std::max(1, std::min<int>(16, (int)(cfg.B / 2 / BITS_BS)));
-    int nbits = cfg.W * cfg.c;
-    P* slices = (P*)ctx.workspace("msm.slices", (size_t)nbits * S * sizeof(P));
-    P* bits = (P*)ctx.workspace("msm.bits." + slot, (size_t)nbits * sizeof(P));
-    dim3 grid(S, cfg.c, cfg.W);
-    UG_KERNEL(ctx, (sizeof(F) == 32 ? "k_bucket_bits<G1>" : "k_bucket_bits<G2>"), k_bucket_bits<F><<<grid, BITS_BS, 0, ctx.stream>>>(buckets, cfg.c, S, slices));
-    UG_KERNEL(ctx, (sizeof(F) == 32 ? "k_sum_slices<G1>" : "k_sum_slices<G2>"), k_sum_slices<F><<<(nbits + 63) / 64, 64, 0, ctx.stream>>>(slices, S, nbits, bits));
-    // pinned result slot: nbits partial sums, then the number of digit entries this MSM processed (a counter
+    // bucket reduction: chunked running sums, recursively on the chunk sums; out[level][window]
+    const MsmReducePlan plan = msm_reduce_plan(cfg);
+    const int nwin = cfg.nwin(), L = plan.levels();
+    const uint32_t K0 = plan.K[0];
+    P* Sbuf[2] = {(P*)ctx.workspace("msm.Sa", (size_t)nwin * K0 * sizeof(P)), (P*)ctx.workspace("msm.Sb", (size_t)nwin * K0 * sizeof(P))};
+    P* R = (P*)ctx.workspace("msm.R", (size_t)nwin * K0 * sizeof(P));
+    P* Rpart = (P*)ctx.workspace("msm.Rpart", (size_t)nwin * 64 * sizeof(P));
+    P* sums = (P*)ctx.workspace("msm.sums." + slot, (size_t)L * nwin * sizeof(P));
+    const P* X = buckets;
+    uint32_t strideX = cfg.B;
+    for (int l = 0; l < L; l++) {
+        const uint32_t N = plan.N[l], Kl = plan.K[l];
+        P* S = Sbuf[l & 1];
+        dim3 grid((Kl + 127) / 128, nwin);
+        UG_KERNEL(ctx, (g1 ? "k_running_sum<G1>" : "k_running_sum<G2>"), k_running_sum<F><<<grid, 128, 0, ctx.stream>>>(X, N, strideX, 1u << plan.mu, Kl, S, R));
+        const uint32_t G = std::min<uint32_t>(64, (Kl + SUM_BS - 1) / SUM_BS);
+        if (G > 1) {
+            UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(G, nwin), SUM_BS, 0, ctx.stream>>>(R, Kl, Kl, Rpart));
+            UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(1, nwin), SUM_BS, 0, ctx.stream>>>(Rpart, G, G, sums + (size_t)l * nwin));
+        } else {
+            UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(1, nwin), SUM_BS, 0, ctx.stream>>>(R, Kl, Kl, sums + (size_t)l * nwin));
+        }
+        X = S + 1;  // weights 1..K-1 on chunk sums 1..K-1
+        strideX = Kl;
+    }
+    // pinned result slot: L*nwin partial sums, then the number of digit entries this MSM processed (a counter
     // for the roofline arithmetic: every entry is one 4-byte index + one affine point gather + one mixed add)
-    uint8_t* host = (uint8_t*)ctx.pinned("msm.bits." + slot, (size_t)nbits * sizeof(P) + 16);
-    UG_CUDA_CHECK(cudaMemcpyAsync(host, bits, (size_t)nbits * sizeof(P), cudaMemcpyDeviceToHost, ctx.stream));
-    UG_CUDA_CHECK(cudaMemcpyAsync(host + (size_t)nbits * sizeof(P), dg.starts + cfg.NB, 4, cudaMemcpyDeviceToHost, ctx.stream));
+    const size_t bytes = (size_t)L * nwin * sizeof(P);
+    uint8_t* host = (uint8_t*)ctx.pinned("msm.sums." + slot, (size_t)64 * 32 * sizeof(P) + 16);
+    if (bytes > (size_t)64 * 32 * sizeof(P)) throw std::runtime_error("ultragroth_b200: MSM reduction plan too deep");
+    UG_CUDA_CHECK(cudaMemcpyAsync(host, sums, bytes, cudaMemcpyDeviceToHost, ctx.stream));
+    UG_CUDA_CHECK(cudaMemcpyAsync(host + bytes, dg.starts + cfg.NB, 4, cudaMemcpyDeviceToHost, ctx.stream));
     ctx.record("msm." + slot);
 }
 
@@ -126,5 +172,35 @@ void msm_g1_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, con
 }
 void msm_g2_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot) {
     msm_launch_impl<Fq2>(ctx, (const G2Affine*)d_bases, dg, slot);
+}
+
+// ---- resident window tables ----------------------------------------------------------------------
+template <class F>
+static void* build_table_impl(DeviceCtx& ctx, const Affine<F>* d_bases, uint64_t n, const MsmConfig& cfg) {
+    ctx.activate();
+    Affine<F>* table = nullptr;
+    const size_t level_bytes = (size_t)n * sizeof(Affine<F>);
+    UG_CUDA_CHECK(cudaMalloc((void**)&table, std::max<size_t>(level_bytes * cfg.W, 16)));
+    if (n == 0) return table;
+    UG_CUDA_CHECK(cudaMemcpyAsync(table, d_bases, level_bytes, cudaMemcpyDeviceToDevice, ctx.stream));
+    XYZZ<F>* tmp = (XYZZ<F>*)ctx.workspace("msm.table_tmp", (size_t)n * sizeof(XYZZ<F>));
+    const int blocks = (int)std::min<uint64_t>((n + 127) / 128, (uint64_t)ctx.sm_count * 8);
+    const int blocks_aff = (int)std::min<uint64_t>((n + 128 * AFF_RUN - 1) / (128 * AFF_RUN), (uint64_t)ctx.sm_count * 8);
+    for (int w = 1; w < cfg.W; w++) {
+        UG_KERNEL(ctx, "k_table_shift", k_table_shift<F><<<blocks, 128, 0, ctx.stream>>>(table + (size_t)(w - 1) * n, (uint32_t)n, cfg.c, tmp));
+        UG_KERNEL(ctx, "k_batch_to_affine", k_batch_to_affine<F><<<std::max(blocks_aff, 1), 128, 0, ctx.stream>>>(tmp, (uint32_t)n, table + (size_t)w * n));
+    }
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+    return table;
+}
+
+MsmTable msm_build_table(DeviceCtx& ctx, int group, const void* d_bases, uint64_t n, int force_c) {
+    MsmTable t;
+    t.n = n;
+    t.cfg = msm_pick_config(n, force_c, true);
+    if ((uint64_t)n * t.cfg.W >= (1ull << 31)) throw std::runtime_error("ultragroth_b200: MSM table too large for 31-bit indices");
+    t.d_table = group == 1 ? build_table_impl<Fq>(ctx, (const G1Affine*)d_bases, n, t.cfg)
+                           : build_table_impl<Fq2>(ctx, (const G2Affine*)d_bases, n, t.cfg);
+    return t;
 }
 }  // namespace ug

@@ -14,9 +14,10 @@
 //                         unbalance it), adds affine points into an XYZZ accumulator and flushes at
 //                         bucket boundaries; runs cut by a slice boundary become (key, partial) pairs
 //   5. k_seg_reduce       segmented scan over those pairs (recursively, 128:2 per level)
-//   6. k_bucket_bits      U[p] = sum of buckets whose weight has bit p set (pure tree reductions)
-//   7. host               sum_p 2^p U[p] by Horner (255 doublings) -- O(1) serial work, as the
-//                         reference's own final double-and-add (north star: "reduced on the host")
+//   6. k_running_sum      chunked running sums over every window's buckets, recursively on the chunk sums
+//      k_sum_points       (2 additions per bucket), leaving a handful of partial sums per window
+//   7. host               Horner over the levels and the windows (a few hundred doublings) -- O(1) serial
+//                         work, as the reference's own final double-and-add (north star: "reduced on the host")
 #pragma once
 #include "curve.cuh"
 #include "memops.cuh"
@@ -79,26 +80,28 @@ UG_D Scalar256 load_scalar(const uint8_t* scalars, const uint32_t* index, uint64
 
 #if defined(__CUDACC__)
 
+// key_stride / entry_stride select the bucket layout:
+//   per-window bucket sets (ad-hoc bases):   key = w*B + |d|-1,  entry = i                 (key_stride = B, entry_stride = 0)
+//   one shared bucket set (precomputed 2^(c*w) multiples of every base, msm_build_table):
+//                                            key = |d|-1,        entry = w*n_bases + i     (key_stride = 0, entry_stride = n_bases)
 __global__ void k_digits_count(const uint8_t* __restrict__ scalars, const uint32_t* __restrict__ index,
-                               uint64_t n, int c, int W, uint32_t* __restrict__ counts) {
-    const uint32_t B = 1u << (c - 1);
+                               uint64_t n, int c, int W, uint32_t key_stride, uint32_t* __restrict__ counts) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
         Scalar256 s = load_scalar(scalars, index, i);
         scalar_reduce(s);
-        scalar_digits(s, c, W, [&](int w, uint32_t b, bool) { atomicAdd(&counts[(uint32_t)w * B + b], 1u); });
+        scalar_digits(s, c, W, [&](int w, uint32_t b, bool) { atomicAdd(&counts[(uint32_t)w * key_stride + b], 1u); });
     }
 }
 
 __global__ void k_digits_scatter(const uint8_t* __restrict__ scalars, const uint32_t* __restrict__ index,
-                                 uint64_t n, int c, int W, uint32_t* __restrict__ cursor,
-                                 uint32_t* __restrict__ entries) {
-    const uint32_t B = 1u << (c - 1);
+                                 uint64_t n, int c, int W, uint32_t key_stride, uint32_t entry_stride,
+                                 uint32_t* __restrict__ cursor, uint32_t* __restrict__ entries) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
         Scalar256 s = load_scalar(scalars, index, i);
         scalar_reduce(s);
         scalar_digits(s, c, W, [&](int w, uint32_t b, bool neg) {
-            uint32_t pos = atomicAdd(&cursor[(uint32_t)w * B + b], 1u);
-            entries[pos] = (uint32_t)i | (neg ? 0x80000000u : 0u);
+            uint32_t pos = atomicAdd(&cursor[(uint32_t)w * key_stride + b], 1u);
+            entries[pos] = ((uint32_t)i + (uint32_t)w * entry_stride) | (neg ? 0x80000000u : 0u);
         });
     }
 }
@@ -270,45 +273,99 @@ __global__ void __launch_bounds__(SEG_BS) k_seg_reduce(const uint32_t* __restric
     }
 }
 
-// ---- bucket reduction: U[w*c + k] = sum over buckets j of window w whose weight (j+1) has bit k set
-constexpr int BITS_BS = 128;
-
+// ---- bucket reduction by chunked running sums ---------------------------------------------------
+// One window's result is sum_j (j+1) * X[j] over its N buckets.  Thread k owns the chunk [k*m, (k+1)*m) and walks it
+// from the top with the classic running sum (2 additions per bucket):
+//     S[k] = sum X[j],      R[k] = sum (j - k*m + 1) * X[j]
+// so that   sum_j (j+1) X[j] = sum_k R[k] + m * sum_k k * S[k],   and the second term is the same problem on
+// S[1..K-1] -- the host recurses (msm.cu) and applies the powers of m = 2^mu by doublings at the very end.
+// blockIdx.y selects the window (independent bucket arrays `strideX` apart).
 template <class F>
-__global__ void __launch_bounds__(BITS_BS) k_bucket_bits(const XYZZ<F>* __restrict__ buckets, int c, int S,
-                                                         XYZZ<F>* __restrict__ out /* [W][c][S] */) {
-    __shared__ XYZZ<F> sh[BITS_BS];
-    const int s = blockIdx.x, k = blockIdx.y, w = blockIdx.z;
-    const uint32_t B = 1u << (c - 1);
-    const XYZZ<F>* wb = buckets + (size_t)w * B;
-    XYZZ<F> acc = XYZZ<F>::inf();
-    if (k == c - 1) {
-        if (s == 0 && threadIdx.x == 0) acc = ld_g(&wb[B - 1]);
-    } else {
-        const uint32_t half = B >> 1;               // number of weights < B with bit k set
-        const uint32_t per = (half + S - 1) / S;
-        const uint32_t m_lo = s * per, m_hi = min(half, m_lo + per);
-        for (uint32_t m = m_lo + threadIdx.x; m < m_hi; m += BITS_BS) {
-            uint32_t v = ((m >> k) << (k + 1)) | (1u << k) | (m & ((1u << k) - 1u));
-            XYZZ<F> p = ld_g(&wb[v - 1]);
-            pt_add(acc, p);
-        }
+__global__ void __launch_bounds__(128) k_running_sum(const XYZZ<F>* __restrict__ X, uint32_t N, uint32_t strideX, uint32_t m,
+                                                     uint32_t K, XYZZ<F>* __restrict__ S, XYZZ<F>* __restrict__ R) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K) return;
+    const XYZZ<F>* x = X + (size_t)blockIdx.y * strideX;
+    const uint32_t lo = k * m, hi = min(N, lo + m);
+    XYZZ<F> acc = XYZZ<F>::inf(), sum = XYZZ<F>::inf();
+    for (uint32_t j = hi; j-- > lo;) {
+        XYZZ<F> p = ld_g(&x[j]);
+        pt_add(acc, p);
+        pt_add(sum, acc);
     }
-    for (int d = BITS_BS / 2; d > 0; d >>= 1) {
+    st_g(&S[(size_t)blockIdx.y * K + k], acc);
+    st_g(&R[(size_t)blockIdx.y * K + k], sum);
+}
+
+// out[w*G + g] = sum of in[w*strideIn + i] over i = g*BS + tid, stepping by G*BS  (plain sums of the R arrays)
+constexpr int SUM_BS = 128;
+template <class F>
+__global__ void __launch_bounds__(SUM_BS) k_sum_points(const XYZZ<F>* __restrict__ in, uint32_t N, uint32_t strideIn,
+                                                       XYZZ<F>* __restrict__ out) {
+    __shared__ XYZZ<F> sh[SUM_BS];
+    const XYZZ<F>* x = in + (size_t)blockIdx.y * strideIn;
+    XYZZ<F> acc = XYZZ<F>::inf();
+    for (uint32_t i = blockIdx.x * SUM_BS + threadIdx.x; i < N; i += gridDim.x * SUM_BS) {
+        XYZZ<F> p = ld_g(&x[i]);
+        pt_add(acc, p);
+    }
+    for (int d = SUM_BS / 2; d > 0; d >>= 1) {
         sh[threadIdx.x] = acc;
         __syncthreads();
         if (threadIdx.x < d) { XYZZ<F> o = sh[threadIdx.x + d]; pt_add(acc, o); }
         __syncthreads();
     }
-    if (threadIdx.x == 0) st_g(&out[((size_t)w * c + k) * S + s], acc);
+    if (threadIdx.x == 0) st_g(&out[(size_t)blockIdx.y * gridDim.x + blockIdx.x], acc);
 }
 
+// ---- precomputed window tables (resident bases only) ---------------------------------------------
+// level k of the table holds 2^(c*k) * P_i in affine form.  k_table_shift: out = 2^c * in (XYZZ, no inversion);
+// k_batch_to_affine: RUN points per thread share one field inversion (Montgomery's trick).
 template <class F>
-__global__ void k_sum_slices(const XYZZ<F>* __restrict__ in, int S, int count, XYZZ<F>* __restrict__ out) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= count) return;
-    XYZZ<F> acc = ld_g(&in[(size_t)i * S]);
-    for (int s = 1; s < S; s++) { XYZZ<F> p = ld_g(&in[(size_t)i * S + s]); pt_add(acc, p); }
-    st_g(&out[i], acc);
+__global__ void __launch_bounds__(128) k_table_shift(const Affine<F>* __restrict__ in, uint32_t n, int c, XYZZ<F>* __restrict__ out) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        Affine<F> a = ld_nc(&in[i]);
+        XYZZ<F> p = pt_dbl_affine(a);
+        for (int k = 1; k < c; k++) p = pt_dbl(p);
+        st_g(&out[i], p);
+    }
+}
+
+constexpr int AFF_RUN = 8;
+template <class F>
+__global__ void __launch_bounds__(128) k_batch_to_affine(const XYZZ<F>* __restrict__ in, uint32_t n, Affine<F>* __restrict__ out) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t T = gridDim.x * blockDim.x;
+    // thread t owns points t, t+T, t+2T, ... (coalesced), AFF_RUN at a time
+    for (uint32_t base = t; base < n; base += T * AFF_RUN) {
+        F pre[AFF_RUN];
+        F acc = F::one();
+#pragma unroll
+        for (int k = 0; k < AFF_RUN; k++) {
+            const uint32_t i = base + k * T;
+            pre[k] = acc;
+            if (i < n) {
+                F z = ld_g(&in[i].ZZZ);
+                if (!z.is_zero()) acc = fmul(acc, z);
+            }
+        }
+        F inv = finv(acc);
+#pragma unroll
+        for (int k = AFF_RUN - 1; k >= 0; k--) {
+            const uint32_t i = base + k * T;
+            if (i >= n) continue;
+            XYZZ<F> p = ld_g(&in[i]);
+            Affine<F> a = Affine<F>::inf();
+            if (!p.ZZZ.is_zero()) {
+                F izzz = fmul(inv, pre[k]);
+                inv = fmul(inv, p.ZZZ);
+                F izz = fsqr(fmul(izzz, p.ZZ));  // (ZZ/ZZZ)^2 = 1/ZZ
+                a.x = fmul(p.X, izz);
+                a.y = fmul(p.Y, izzz);
+            }
+            st_g(&out[i], a);
+        }
+    }
 }
 
 #endif  // __CUDACC__

@@ -4,6 +4,8 @@
 #include "device.hpp"
 #include "host_ff.hpp"
 
+#include <vector>
+
 namespace ug {
 
 using HG1Affine = Affine<HFq>;
@@ -15,32 +17,56 @@ struct MsmConfig {
     int c = 0;        // window bits
     int W = 0;        // windows = ceil(255 / c)
     uint32_t B = 0;   // buckets per window = 2^(c-1)
-    uint32_t NB = 0;  // W * B
+    uint32_t NB = 0;  // bucket count: W * B, or B when `pre`
+    bool pre = false; // bases come with precomputed 2^(c*w) multiples (msm_build_table): ONE bucket set for all windows
+    int nwin() const { return pre ? 1 : W; }
 };
 
-MsmConfig msm_pick_config(uint64_t n, int force_c = 0);
+// pre = false: per-window bucket sets (any base array); pre = true: the window size for a resident table over n bases
+MsmConfig msm_pick_config(uint64_t n, int force_c = 0, bool pre = false);
+
+// Bucket-reduction schedule (chunked running sums, msm.cuh): level l turns N[l] buckets per window into K[l] chunk sums.
+struct MsmReducePlan {
+    int mu = 0;                      // chunk = 2^mu buckets
+    std::vector<uint32_t> N, K;      // per level
+    int levels() const { return (int)N.size(); }
+};
+MsmReducePlan msm_reduce_plan(const MsmConfig& cfg);
+
+// Resident bases with their window multiples: table[w*n + i] = 2^(c*w) * base[i], affine, zkey layout.
+// Costs W times the memory of the base array (HBM is 180 GB) and removes W-1 of the W bucket reductions; with the
+// reduction this cheap the window grows from c = 16 to c = 22 at n = 2^22, i.e. 12 instead of 16 additions per point.
+struct MsmTable {
+    void* d_table = nullptr;  // cudaMalloc'ed, owned by the caller (ProverDevice)
+    uint64_t n = 0;
+    MsmConfig cfg;
+};
+// Builds the table on the device from n affine bases (device pointer).  group 1 = G1 (64 B), 2 = G2 (128 B).
+MsmTable msm_build_table(DeviceCtx& ctx, int group, const void* d_bases, uint64_t n, int force_c = 0);
 
 // Sorted signed digits of one scalar vector; reusable for every base array that pairs with it
 // (A, B1, B2 and the shifted C all multiply the same witness, src/groth16.cpp:55-64).
 struct MsmDigits {
     MsmConfig cfg;
     uint64_t n = 0;
-    uint32_t* entries = nullptr;  // [<= n*W] point index | sign<<31, grouped by (window, |digit|-1)
+    uint32_t* entries = nullptr;  // [<= n*W] point (or table) index | sign<<31, grouped by bucket key
     uint32_t* starts = nullptr;   // [NB+1] offsets, starts[NB] = number of entries
 };
 
 // d_scalars: n (or max(index)+1) raw 32-byte little-endian scalars on the device; d_index optional gather
 // list (src/ultra_groth.cpp:415-419,439-445 folded into the scalar fetch).  `slot` names the workspace.
+// `table_cfg`: when the digits are meant for MsmTable bases, the table's config (window size and layout must match).
 void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d_index, uint64_t n, int force_c,
-                     const std::string& slot, MsmDigits& out);
+                     const std::string& slot, MsmDigits& out, const MsmConfig* table_cfg = nullptr);
 
 // Bucket accumulation + bucket reduction on the device for one base array, final Horner on the host.
 void msm_accumulate_g1(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, HG1XYZZ* out);
 void msm_accumulate_g2(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, HG2XYZZ* out);
 
 // Asynchronous halves (so that several MSMs can be queued before the first host combine):
-// *_launch enqueues everything up to the D2H copy of the per-bit sums into pinned slot `slot`;
-// *_finish waits for the stream and runs the Horner combine.
+// *_launch enqueues everything up to the D2H copy of the per-level partial sums into pinned slot `slot`;
+// *_finish waits for the stream and runs the Horner combine.  d_bases is the plain base array, or MsmTable::d_table
+// when the digits were sorted for that table.
 void msm_g1_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot);
 void msm_g1_finish(DeviceCtx& ctx, const MsmDigits& dg, const std::string& slot, HG1XYZZ* out);
 void msm_g2_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot);

@@ -1,5 +1,5 @@
-// Host half of the MSM: wait for the per-bit partial sums and combine them, sum_p 2^p U[p], by Horner.
-// O(W*c) = 255 doublings + additions on the CPU -- the serial tail the reference also runs on the CPU.
+// Host half of the MSM: wait for the per-level / per-window partial sums of the running-sum reduction and combine
+// them by Horner: a few hundred doublings on the CPU -- the serial tail the reference also runs on the CPU.
 #include "msm.hpp"
 
 #include <cstring>
@@ -9,15 +9,22 @@ namespace ug {
 template <class HF>
 static void msm_finish_impl(DeviceCtx& ctx, const MsmDigits& dg, const std::string& slot, XYZZ<HF>* out) {
     ctx.wait("msm." + slot);
-    int nbits = dg.cfg.W * dg.cfg.c;
-    const XYZZ<HF>* U = (const XYZZ<HF>*)ctx.pinned("msm.bits." + slot, (size_t)nbits * sizeof(XYZZ<HF>) + 16);
+    const MsmReducePlan plan = msm_reduce_plan(dg.cfg);
+    const int nwin = dg.cfg.nwin(), L = plan.levels();
+    const XYZZ<HF>* U = (const XYZZ<HF>*)ctx.pinned("msm.sums." + slot, (size_t)64 * 32 * sizeof(XYZZ<HF>) + 16);
     uint32_t entries = 0;
-    memcpy(&entries, (const uint8_t*)U + (size_t)nbits * sizeof(XYZZ<HF>), 4);
+    memcpy(&entries, (const uint8_t*)U + (size_t)L * nwin * sizeof(XYZZ<HF>), 4);
     if (ctx.profile) ctx.counters[sizeof(HF) == 32 ? "#msm_entries<G1>" : "#msm_entries<G2>"] += entries;
+    // window w: sum_l 2^(mu*l) * U[l][w]; windows: sum_w 2^(c*w) * (...), both by Horner
     XYZZ<HF> acc = XYZZ<HF>::inf();
-    for (int p = nbits - 1; p >= 0; p--) {
-        acc = pt_dbl(acc);
-        pt_add(acc, U[p]);
+    for (int w = nwin - 1; w >= 0; w--) {
+        for (int k = 0; k < dg.cfg.c; k++) acc = pt_dbl(acc);
+        XYZZ<HF> win = XYZZ<HF>::inf();
+        for (int l = L - 1; l >= 0; l--) {
+            for (int k = 0; k < plan.mu; k++) win = pt_dbl(win);
+            pt_add(win, U[(size_t)l * nwin + w]);
+        }
+        pt_add(acc, win);
     }
     *out = acc;
 }

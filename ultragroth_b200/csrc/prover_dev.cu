@@ -265,6 +265,27 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
         coef_val_ = upload(ctx, val.data(), val.size());
         UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
     }
+    // window tables: 2^(c*w) multiples of every base, resident next to the bases they replace (UGB_MSM_PRE=0: off)
+    {
+        const char* e = getenv("UGB_MSM_PRE");
+        pre_ = !(e && atoi(e) == 0);
+        if (pre_) {
+            auto tabulate = [&](void*& base, int group, uint64_t count, MsmConfig& cfg) {
+                MsmTable t = msm_build_table(ctx, group, base, count);
+                UG_CUDA_CHECK(cudaFree(base));
+                base = t.d_table;
+                cfg = t.cfg;
+            };
+            MsmConfig tmp;
+            tabulate(A_, 1, nVars, cfg_w_);
+            tabulate(B1_, 1, nVars, tmp);
+            tabulate(B2_, 2, nVars, tmp);
+            if (c_shares_witness_sort_) tabulate(C_, 1, nVars, tmp);
+            else tabulate(C_, 1, n_c2_, cfg_c2_);
+            tabulate(H_, 1, domainSize, cfg_h_);
+            if (ultra_) tabulate(C1_, 1, n_c1_, cfg_c1_);
+        }
+    }
     w_ = dev_alloc((size_t)nVars * 32);
     a_ = dev_alloc((size_t)domainSize * 32);
     b_ = dev_alloc((size_t)domainSize * 32);
@@ -311,7 +332,7 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     mark();  // 0
     // the four witness MSMs share one digit sort (src/groth16.cpp:53-64 all read the same scalars)
     MsmDigits dw;
-    msm_sort_digits(ctx, (const uint8_t*)w_, nullptr, nVars, 0, "w", dw);
+    msm_sort_digits(ctx, (const uint8_t*)w_, nullptr, nVars, 0, "w", dw, pre_ ? &cfg_w_ : nullptr);
     mark();  // 1
     msm_g1_launch(ctx, A_, dw, "a");
     mark();  // 2
@@ -323,7 +344,7 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     if (c_shares_witness_sort_) {
         msm_g1_launch(ctx, C_, dw, "c");
     } else {
-        msm_sort_digits(ctx, (const uint8_t*)w_, idx_c2_, n_c2_, 0, "cidx", dc);
+        msm_sort_digits(ctx, (const uint8_t*)w_, idx_c2_, n_c2_, 0, "cidx", dc, pre_ ? &cfg_c2_ : nullptr);
         msm_g1_launch(ctx, C_, dc, "c");
     }
     mark();  // 5
@@ -344,7 +365,7 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     UG_KERNEL(ctx, "k_h_final", k_h_final<<<blocks, 256, 0, ctx.stream>>>((Fr*)a_, (const Fr*)b_, (const Fr*)c_, n));
     mark();  // 9
     MsmDigits dh;
-    msm_sort_digits(ctx, (const uint8_t*)a_, nullptr, n, 0, "h", dh);
+    msm_sort_digits(ctx, (const uint8_t*)a_, nullptr, n, 0, "h", dh, pre_ ? &cfg_h_ : nullptr);
     mark();  // 10
     msm_g1_launch(ctx, H_, dh, "h");
     mark();  // 11
@@ -386,7 +407,7 @@ void ProverDevice::ultra_round_msm(HG1XYZZ& out) {
     ctx.activate();
     // round_wtns[i] = wtns[round_indexes[i]] (src/ultra_groth.cpp:415-419) folded into the scalar fetch
     MsmDigits d;
-    msm_sort_digits(ctx, (const uint8_t*)w_, idx_c1_, n_c1_, 0, "round", d);
+    msm_sort_digits(ctx, (const uint8_t*)w_, idx_c1_, n_c1_, 0, "round", d, pre_ ? &cfg_c1_ : nullptr);
     msm_g1_launch(ctx, C1_, d, "round");
     msm_g1_finish(ctx, d, "round", &out);
 }

@@ -66,6 +66,9 @@ private:
     // bases
     void *A_ = nullptr, *B1_ = nullptr, *B2_ = nullptr, *C_ = nullptr, *H_ = nullptr, *C1_ = nullptr;
     bool c_shares_witness_sort_ = false;
+    // resident window tables (msm_build_table): every *_ base pointer above then holds W levels instead of one
+    bool pre_ = false;
+    MsmConfig cfg_w_, cfg_h_, cfg_c1_, cfg_c2_;
     uint32_t *idx_c1_ = nullptr, *idx_c2_ = nullptr;
     // coefficient matrix, CSR by (matrix, row)
     uint32_t* row_ptr_ = nullptr;  // [2n + 1]
