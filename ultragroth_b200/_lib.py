@@ -7,7 +7,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libultragroth_b200.so")
+LIB_PATH = os.environ.get("UGB_LIB") or os.path.join(_HERE, "libultragroth_b200.so")
 
 _lib = None
 

@@ -9,12 +9,15 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(HERE, "libultragroth_b200.so")
-OBJ = os.path.join(HERE, "build")
+# experiment builds: UGB_BUILD_TAG=x UGB_BUILD_DEFS="-DUG_FOO" -> libultragroth_b200_x.so (load it with UGB_LIB=<path>)
+TAG = os.environ.get("UGB_BUILD_TAG", "")
+OUT = os.path.join(HERE, "libultragroth_b200%s.so" % ("_" + TAG if TAG else ""))
+OBJ = os.path.join(HERE, "build" + ("_" + TAG if TAG else ""))
+EXTRA_DEFS = os.environ.get("UGB_BUILD_DEFS", "").split()
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
-              "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"]
+              "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"] + EXTRA_DEFS
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-I/usr/local/cuda/include"]
 
 

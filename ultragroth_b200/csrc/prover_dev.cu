@@ -41,22 +41,39 @@ constexpr uint32_t SPMV_LONG_ROW = 48;
 constexpr int SPMV_LONG_BS = 512;
 struct LongRow { uint32_t slot /* m*n + row */, lo, hi; };
 
-__global__ void __launch_bounds__(SPMV_LONG_BS) k_spmv_long(const LongRow* __restrict__ rows, const uint32_t* __restrict__ sig,
-                                                            const Fr* __restrict__ coef, const Fr* __restrict__ w, uint32_t n,
-                                                            Fr* __restrict__ a, Fr* __restrict__ b) {
-    __shared__ Fr sh[SPMV_LONG_BS];
-    const LongRow r = rows[blockIdx.x];
-    Fr acc = Fr::zero();
-    for (uint32_t k = r.lo + threadIdx.x; k < r.hi; k += SPMV_LONG_BS) acc = fp_add(acc, fp_mul(ld_nc(&w[sig[k]]), ld_nc(&coef[k])));
+// pass 1: one CTA per SEGMENT (<= SPMV_SEG terms) of a long row -> partial[seg]; pass 2 (k_spmv_long_finish): one CTA per
+// long row sums its partials.  A 2^20-term lookup row is 128 CTAs instead of one.
+constexpr uint32_t SPMV_SEG = 8192;
+__device__ __forceinline__ Fr block_sum_fr(Fr acc, Fr* sh) {
     sh[threadIdx.x] = acc;
     __syncthreads();
     for (int d = SPMV_LONG_BS / 2; d > 0; d >>= 1) {
         if ((int)threadIdx.x < d) sh[threadIdx.x] = fp_add(sh[threadIdx.x], sh[threadIdx.x + d]);
         __syncthreads();
     }
+    return sh[0];
+}
+__global__ void __launch_bounds__(SPMV_LONG_BS) k_spmv_long(const LongRow* __restrict__ segs, const uint32_t* __restrict__ sig,
+                                                            const Fr* __restrict__ coef, const Fr* __restrict__ w,
+                                                            Fr* __restrict__ partial) {
+    __shared__ Fr sh[SPMV_LONG_BS];
+    const LongRow r = segs[blockIdx.x];
+    Fr acc = Fr::zero();
+    for (uint32_t k = r.lo + threadIdx.x; k < r.hi; k += SPMV_LONG_BS) acc = fp_add(acc, fp_mul(ld_nc(&w[sig[k]]), ld_nc(&coef[k])));
+    Fr tot = block_sum_fr(acc, sh);
+    if (threadIdx.x == 0) st_g(&partial[blockIdx.x], tot);
+}
+// rows[i].lo..hi is the SEGMENT range of long row i
+__global__ void __launch_bounds__(SPMV_LONG_BS) k_spmv_long_finish(const LongRow* __restrict__ rows, const Fr* __restrict__ partial,
+                                                                   uint32_t n, Fr* __restrict__ a, Fr* __restrict__ b) {
+    __shared__ Fr sh[SPMV_LONG_BS];
+    const LongRow r = rows[blockIdx.x];
+    Fr acc = Fr::zero();
+    for (uint32_t k = r.lo + threadIdx.x; k < r.hi; k += SPMV_LONG_BS) acc = fp_add(acc, ld_g(&partial[k]));
+    Fr tot = block_sum_fr(acc, sh);
     if (threadIdx.x == 0) {
-        if (r.slot < n) st_g(&a[r.slot], sh[0]);
-        else st_g(&b[r.slot - n], sh[0]);
+        if (r.slot < n) st_g(&a[r.slot], tot);
+        else st_g(&b[r.slot - n], tot);
     }
 }
 __global__ void k_spmv_fix_c(const LongRow* __restrict__ rows, uint32_t count, uint32_t n, const Fr* __restrict__ a,
@@ -238,13 +255,15 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
         }
         // short rows form the CSR proper; long rows keep an empty CSR row and live after `short_total`
         std::vector<uint32_t> rp((size_t)2 * n + 1, 0);
-        std::vector<LongRow> longs;
+        std::vector<LongRow> longs, segs;
         for (size_t i = 0; i < (size_t)2 * n; i++) rp[i + 1] = rp[i] + (len[i] > SPMV_LONG_ROW ? 0 : len[i]);
         uint32_t tail = rp[(size_t)2 * n];
         std::vector<uint32_t> cur(rp.begin(), rp.end() - 1);
         for (size_t i = 0; i < (size_t)2 * n; i++) {
             if (len[i] > SPMV_LONG_ROW) {
-                longs.push_back(LongRow{(uint32_t)i, tail, tail + len[i]});
+                const uint32_t seg0 = (uint32_t)segs.size();
+                for (uint32_t o = 0; o < len[i]; o += SPMV_SEG) segs.push_back(LongRow{(uint32_t)i, tail + o, tail + std::min(len[i], o + SPMV_SEG)});
+                longs.push_back(LongRow{(uint32_t)i, seg0, (uint32_t)segs.size()});
                 cur[i] = tail;
                 tail += len[i];
             }
@@ -259,7 +278,12 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
             memcpy(&val[(size_t)pos * 32], rec + k * 44 + 12, 32);
         }
         n_long_ = (uint32_t)longs.size();
-        if (n_long_) long_rows_ = upload(ctx, longs.data(), longs.size() * sizeof(LongRow));
+        n_long_segs_ = (uint32_t)segs.size();
+        if (n_long_) {
+            long_rows_ = upload(ctx, longs.data(), longs.size() * sizeof(LongRow));
+            long_segs_ = upload(ctx, segs.data(), segs.size() * sizeof(LongRow));
+            long_partial_ = dev_alloc((size_t)n_long_segs_ * 32);
+        }
         row_ptr_ = (uint32_t*)upload(ctx, rp.data(), rp.size() * 4);
         coef_sig_ = (uint32_t*)upload(ctx, sig.data(), sig.size() * 4);
         coef_val_ = upload(ctx, val.data(), val.size());
@@ -305,7 +329,7 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
 ProverDevice::~ProverDevice() {
     cudaSetDevice(ctx_->device);
     cudaStreamSynchronize(ctx_->stream);
-    for (void* p : {long_rows_, A_, B1_, B2_, C_, H_, C1_, (void*)idx_c1_, (void*)idx_c2_, (void*)row_ptr_, (void*)coef_sig_, coef_val_, w_, a_, b_, c_})
+    for (void* p : {long_rows_, long_segs_, long_partial_, A_, B1_, B2_, C_, H_, C1_, (void*)idx_c1_, (void*)idx_c2_, (void*)row_ptr_, (void*)coef_sig_, coef_val_, w_, a_, b_, c_})
         if (p) cudaFree(p);
     for (auto& e : ev_) cudaEventDestroy(e);
 }
@@ -352,7 +376,8 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     int blocks = (int)std::min<uint64_t>(((uint64_t)n + 255) / 256, (uint64_t)ctx.sm_count * 8);
     UG_KERNEL(ctx, "k_spmv_abc", k_spmv_abc<<<blocks, 256, 0, ctx.stream>>>(row_ptr_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, n, (Fr*)a_, (Fr*)b_, (Fr*)c_));
     if (n_long_) {
-        UG_KERNEL(ctx, "k_spmv_long", k_spmv_long<<<n_long_, SPMV_LONG_BS, 0, ctx.stream>>>((const LongRow*)long_rows_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, n, (Fr*)a_, (Fr*)b_));
+        UG_KERNEL(ctx, "k_spmv_long", k_spmv_long<<<n_long_segs_, SPMV_LONG_BS, 0, ctx.stream>>>((const LongRow*)long_segs_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, (Fr*)long_partial_));
+        UG_KERNEL(ctx, "k_spmv_long_finish", k_spmv_long_finish<<<n_long_, SPMV_LONG_BS, 0, ctx.stream>>>((const LongRow*)long_rows_, (const Fr*)long_partial_, n, (Fr*)a_, (Fr*)b_));
         UG_KERNEL(ctx, "k_spmv_fix_c", k_spmv_fix_c<<<(n_long_ + 127) / 128, 128, 0, ctx.stream>>>((const LongRow*)long_rows_, n_long_, n, (const Fr*)a_, (const Fr*)b_, (Fr*)c_));
     }
     mark();  // 6

@@ -77,6 +77,9 @@ private:
     uint64_t nCoefs_ = 0;
     void* long_rows_ = nullptr;  // rows too long for one thread (see k_spmv_long)
     uint32_t n_long_ = 0;
+    void* long_segs_ = nullptr;     // the long rows cut into <= SPMV_SEG-term segments, one CTA each
+    void* long_partial_ = nullptr;  // one Fr partial sum per segment
+    uint32_t n_long_segs_ = 0;
     // per-proof buffers
     void *w_ = nullptr, *a_ = nullptr, *b_ = nullptr, *c_ = nullptr;
     std::vector<cudaEvent_t> ev_;
