@@ -7,6 +7,9 @@
 
 namespace ug {
 
+// default kernel variants (0 = all-register kernels; n = shared-memory accumulators at n CTAs per SM), see msm.cuh
+constexpr int ACC_VARIANT_G1 = 0, ACC_VARIANT_G2 = 12, RS_VARIANT_G1 = 0, RS_VARIANT_G2 = 12;
+
 static int env_int_msm(const char* name, int dflt) {
     const char* e = getenv(name);
     return e ? atoi(e) : dflt;
@@ -42,18 +45,14 @@ MsmConfig msm_pick_config(uint64_t n, int force_c, bool pre) {
 
 MsmReducePlan msm_reduce_plan(const MsmConfig& cfg) {
     MsmReducePlan p;
-    // first level: about 64K threads over all windows, chunks of 4..256 buckets
+    // about 64K threads over all windows, chunks of 4..256 buckets
     uint64_t total = (uint64_t)cfg.B * cfg.nwin();
     int mu = 2;
     while (mu < 8 && (total >> mu) > 65536) mu++;
     p.mu = mu;
-    uint32_t N = cfg.B;
-    while (N > 0) {
-        uint32_t K = (N + (1u << mu) - 1) >> mu;
-        p.N.push_back(N);
-        p.K.push_back(K);
-        N = K - 1;  // next level: chunk sums 1..K-1 with weights 1..K-1
-    }
+    p.K = (cfg.B + (1u << mu) - 1) >> mu;
+    p.nbits = 0;
+    while (p.K > 1 && ((p.K - 1) >> p.nbits) != 0) p.nbits++;
     return p;
 }
 
@@ -93,6 +92,58 @@ void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d
     }
 }
 
+// ---- kernel variants ------------------------------------------------------------------------------
+// variant = 0: all-register kernel; n in 2..6: shared-memory accumulators at n CTAs per SM; +10: instantiate on
+// Fqc / Fq2c (called field products, small code) instead of Fq / Fq2 -- same memory layout, so the pointers are only re-typed.
+template <class F> struct AccSig { using Fn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, XYZZ<F>*, uint32_t*, XYZZ<F>*); };
+template <class F> struct RsSig { using Fn = void (*)(const XYZZ<F>*, uint32_t, uint32_t, uint32_t, uint32_t, XYZZ<F>*, XYZZ<F>*); };
+
+template <class G>
+static typename AccSig<G>::Fn pick_acc(int v) {
+    switch (v) {
+        case 0: return k_accumulate<G>;
+        case 2: return k_accumulate_s<G, 2>;
+        case 3: return k_accumulate_s<G, 3>;
+        case 4: return k_accumulate_s<G, 4>;
+        case 5: return k_accumulate_s<G, 5>;
+        case 6: return k_accumulate_s<G, 6>;
+    }
+    throw std::runtime_error("ultragroth_b200: unknown accumulate variant");
+}
+template <class G>
+static typename RsSig<G>::Fn pick_rs(int v) {
+    switch (v) {
+        case 0: return k_running_sum<G>;
+        case 2: return k_running_sum_s<G, 2>;
+        case 3: return k_running_sum_s<G, 3>;
+        case 4: return k_running_sum_s<G, 4>;
+        case 5: return k_running_sum_s<G, 5>;
+    }
+    throw std::runtime_error("ultragroth_b200: unknown running-sum variant");
+}
+template <class F>
+static void select_accumulate(int variant, typename AccSig<F>::Fn& fn, size_t& smem) {
+    const int v = variant % 10;
+    smem = v ? 128 * sizeof(XYZZ<F>) : 0;
+    if constexpr (sizeof(F) == 64) {
+        if (variant >= 10) { fn = (typename AccSig<F>::Fn)pick_acc<Fq2c>(v); return; }
+    } else {
+        if (variant >= 10) { fn = (typename AccSig<F>::Fn)pick_acc<Fqc>(v); return; }
+    }
+    fn = pick_acc<F>(v);
+}
+template <class F>
+static void select_running_sum(int variant, typename RsSig<F>::Fn& fn, size_t& smem) {
+    const int v = variant % 10;
+    smem = v ? 2 * 128 * sizeof(XYZZ<F>) : 0;
+    if constexpr (sizeof(F) == 64) {
+        if (variant >= 10) { fn = (typename RsSig<F>::Fn)pick_rs<Fq2c>(v); return; }
+    } else {
+        if (variant >= 10) { fn = (typename RsSig<F>::Fn)pick_rs<Fqc>(v); return; }
+    }
+    fn = pick_rs<F>(v);
+}
+
 template <class F>
 static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmDigits& dg, const std::string& slot) {
     ctx.activate();
@@ -102,9 +153,15 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     P* buckets = (P*)ctx.workspace("msm.buckets", (size_t)cfg.NB * sizeof(P));
     UG_CUDA_CHECK(cudaMemsetAsync(buckets, 0, (size_t)cfg.NB * sizeof(P), ctx.stream));
 
-    // accumulate: T threads over the sorted entries
+    // accumulate: T threads over the sorted entries.  Kernel variant: the XYZZ accumulator in shared memory at MINB CTAs
+    // per SM (k_accumulate_s), or 0 = all-register k_accumulate.  UGB_ACC_G1 / UGB_ACC_G2 override the default.
+    using AccFn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, P*, uint32_t*, P*);
+    const int acc_variant = env_int_msm(g1 ? "UGB_ACC_G1" : "UGB_ACC_G2", g1 ? ACC_VARIANT_G1 : ACC_VARIANT_G2);
+    AccFn acc_fn = k_accumulate<F>;
+    size_t acc_smem = 0;
+    select_accumulate<F>(acc_variant, acc_fn, acc_smem);
     int occ = 1;
-    UG_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_accumulate<F>, 128, 0));
+    UG_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, acc_fn, 128, acc_smem));
     occ = std::max(occ, 1);
     uint64_t max_entries = dg.n * (uint64_t)cfg.W;
     uint64_t want_threads = std::max<uint64_t>(128, (max_entries + 15) / 16);
@@ -118,7 +175,7 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     uint32_t* keys_b = (uint32_t*)ctx.workspace("msm.pkeys_b", (size_t)K1 * 4);
     P* pts_b = (P*)ctx.workspace("msm.ppts_b", (size_t)K1 * sizeof(P));
 
-    UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), k_accumulate<F><<<blocks, 128, 0, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a));
+    UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), acc_fn<<<blocks, 128, acc_smem, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a));
 
     uint32_t* kin = keys_a; P* pin = pts_a; uint32_t* kout = keys_b; P* pout = pts_b;
     uint32_t Kcur = K;
@@ -132,30 +189,41 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
         std::swap(pin, pout);
     }
 
-    // bucket reduction: chunked running sums, recursively on the chunk sums; out[level][window]
+    // bucket reduction: one level of chunked running sums, then bit-decomposed plain sums of the chunk sums
     const MsmReducePlan plan = msm_reduce_plan(cfg);
-    const int nwin = cfg.nwin(), L = plan.levels();
-    const uint32_t K0 = plan.K[0];
-    P* Sbuf[2] = {(P*)ctx.workspace("msm.Sa", (size_t)nwin * K0 * sizeof(P)), (P*)ctx.workspace("msm.Sb", (size_t)nwin * K0 * sizeof(P))};
+    const int nwin = cfg.nwin(), L = plan.points();
+    const uint32_t K0 = plan.K;
+    P* S = (P*)ctx.workspace("msm.Sa", (size_t)nwin * K0 * sizeof(P));
     P* R = (P*)ctx.workspace("msm.R", (size_t)nwin * K0 * sizeof(P));
-    P* Rpart = (P*)ctx.workspace("msm.Rpart", (size_t)nwin * 64 * sizeof(P));
+    P* Rpart = (P*)ctx.workspace("msm.Rpart", (size_t)nwin * 64 * 33 * sizeof(P));
     P* sums = (P*)ctx.workspace("msm.sums." + slot, (size_t)L * nwin * sizeof(P));
-    const P* X = buckets;
-    uint32_t strideX = cfg.B;
-    for (int l = 0; l < L; l++) {
-        const uint32_t N = plan.N[l], Kl = plan.K[l];
-        P* S = Sbuf[l & 1];
-        dim3 grid((Kl + 127) / 128, nwin);
-        UG_KERNEL(ctx, (g1 ? "k_running_sum<G1>" : "k_running_sum<G2>"), k_running_sum<F><<<grid, 128, 0, ctx.stream>>>(X, N, strideX, 1u << plan.mu, Kl, S, R));
-        const uint32_t G = std::min<uint32_t>(64, (Kl + SUM_BS - 1) / SUM_BS);
+    using RsFn = void (*)(const P*, uint32_t, uint32_t, uint32_t, uint32_t, P*, P*);
+    const int rs_variant = env_int_msm(g1 ? "UGB_RS_G1" : "UGB_RS_G2", g1 ? RS_VARIANT_G1 : RS_VARIANT_G2);
+    RsFn rs_fn = k_running_sum<F>;
+    size_t rs_smem = 0;
+    select_running_sum<F>(rs_variant, rs_fn, rs_smem);
+    if (rs_smem > 48 * 1024) UG_CUDA_CHECK(cudaFuncSetAttribute(rs_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem));
+    {
+        dim3 grid((K0 + 127) / 128, nwin);
+        UG_KERNEL(ctx, (g1 ? "k_running_sum<G1>" : "k_running_sum<G2>"), rs_fn<<<grid, 128, rs_smem, ctx.stream>>>(buckets, cfg.B, cfg.B, 1u << plan.mu, K0, S, R));
+        // sums[0][w] = sum_k R[k]
+        const uint32_t G = std::min<uint32_t>(64, (K0 + SUM_BS - 1) / SUM_BS);
         if (G > 1) {
-            UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(G, nwin), SUM_BS, 0, ctx.stream>>>(R, Kl, Kl, Rpart));
-            UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(1, nwin), SUM_BS, 0, ctx.stream>>>(Rpart, G, G, sums + (size_t)l * nwin));
+            UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(G, nwin), SUM_BS, 0, ctx.stream>>>(R, K0, K0, Rpart));
+            UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(1, nwin), SUM_BS, 0, ctx.stream>>>(Rpart, G, G, sums));
         } else {
-            UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(1, nwin), SUM_BS, 0, ctx.stream>>>(R, Kl, Kl, sums + (size_t)l * nwin));
+            UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(1, nwin), SUM_BS, 0, ctx.stream>>>(R, K0, K0, sums));
         }
-        X = S + 1;  // weights 1..K-1 on chunk sums 1..K-1
-        strideX = Kl;
+        // sums[1+b][w] = sum of S[k] over 1 <= k < K0 with bit b of k set
+        if (plan.nbits > 0) {
+            const uint32_t Gb = std::min<uint32_t>(32, (K0 + 1023) / 1024);
+            if (Gb > 1) {
+                UG_KERNEL(ctx, (g1 ? "k_bit_sums<G1>" : "k_bit_sums<G2>"), k_bit_sums<F><<<dim3(Gb, nwin, plan.nbits), SUM_BS, 0, ctx.stream>>>(S, K0, K0, Rpart));
+                UG_KERNEL(ctx, (g1 ? "k_sum_points<G1>" : "k_sum_points<G2>"), k_sum_points<F><<<dim3(1, nwin * plan.nbits), SUM_BS, 0, ctx.stream>>>(Rpart, Gb, Gb, sums + nwin));
+            } else {
+                UG_KERNEL(ctx, (g1 ? "k_bit_sums<G1>" : "k_bit_sums<G2>"), k_bit_sums<F><<<dim3(1, nwin, plan.nbits), SUM_BS, 0, ctx.stream>>>(S, K0, K0, sums + nwin));
+            }
+        }
     }
     // pinned result slot: L*nwin partial sums, then the number of digit entries this MSM processed (a counter
     // for the roofline arithmetic: every entry is one 4-byte index + one affine point gather + one mixed add)

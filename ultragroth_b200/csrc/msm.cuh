@@ -14,9 +14,9 @@
 //                         unbalance it), adds affine points into an XYZZ accumulator and flushes at
 //                         bucket boundaries; runs cut by a slice boundary become (key, partial) pairs
 //   5. k_seg_reduce       segmented scan over those pairs (recursively, 128:2 per level)
-//   6. k_running_sum      chunked running sums over every window's buckets, recursively on the chunk sums
-//      k_sum_points       (2 additions per bucket), leaving a handful of partial sums per window
-//   7. host               Horner over the levels and the windows (a few hundred doublings) -- O(1) serial
+//   6. k_running_sum      chunked running sums over every window's buckets (2 additions per bucket) -> chunk sums S, R
+//      k_sum_points       sum of the R;   k_bit_sums: sum_k k*S[k] bit by bit (plain tree sums, no serial chain)
+//   7. host               Horner over the bits and the windows (a few hundred doublings) -- O(1) serial
 //                         work, as the reference's own final double-and-add (north star: "reduced on the host")
 #pragma once
 #include "curve.cuh"
@@ -232,6 +232,59 @@ __global__ void __launch_bounds__(128) k_accumulate(const Affine<F>* __restrict_
     }
 }
 
+// Same contract as k_accumulate, with the XYZZ accumulator in shared memory (SmemPoint, curve.cuh) and the next affine
+// point prefetched into registers: MINB CTAs of 128 threads per SM instead of the 2 that 255 registers allow for G2.
+template <class F, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_accumulate_s(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
+                                                            const uint32_t* __restrict__ starts, uint32_t NB,
+                                                            XYZZ<F>* __restrict__ buckets, uint32_t* __restrict__ pkeys,
+                                                            XYZZ<F>* __restrict__ ppts) {
+    extern __shared__ uint4 slab[];
+    const SmemPoint<F, 128> acc{slab + threadIdx.x};
+    const uint32_t T = gridDim.x * blockDim.x;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t M = starts[NB];
+    const uint32_t L = (uint32_t)(((uint64_t)M + T - 1) / T);
+    const uint64_t lo64 = (uint64_t)t * L;
+    if (L == 0 || lo64 >= M) {
+        pkeys[2 * t] = NB; pkeys[2 * t + 1] = NB;
+        st_g(&ppts[2 * t], XYZZ<F>::inf());
+        st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
+        return;
+    }
+    const uint32_t lo = (uint32_t)lo64;
+    const uint32_t hi = (uint32_t)min((uint64_t)M, lo64 + L);
+    uint32_t a = 0, b = NB - 1;
+    while (a < b) {
+        uint32_t mid = (a + b) >> 1;
+        if (starts[mid + 1] > lo) b = mid; else a = mid + 1;
+    }
+    uint32_t key = a;
+    uint32_t end = starts[key + 1];
+    acc.set_inf();
+    bool first = true;
+    uint32_t e = entries[lo];
+    Affine<F> pt = ld_nc(&bases[e & 0x7fffffffu]);
+    for (uint32_t pos = lo; pos < hi; pos++) {
+        if (pos == end) {
+            if (first) { pkeys[2 * t] = key; st_g(&ppts[2 * t], acc.get()); first = false; }
+            else st_g(&buckets[key], acc.get());
+            acc.set_inf();
+            do { key++; end = starts[key + 1]; } while (end <= pos);
+        }
+        const bool neg = (e >> 31) != 0;
+        const Affine<F> cur = pt;
+        if (pos + 1 < hi) { e = entries[pos + 1]; pt = ld_nc(&bases[e & 0x7fffffffu]); }
+        pt_madd_at<F>(acc, cur, neg);
+    }
+    if (first) {
+        pkeys[2 * t] = key; st_g(&ppts[2 * t], acc.get());
+        pkeys[2 * t + 1] = key; st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
+    } else {
+        pkeys[2 * t + 1] = key; st_g(&ppts[2 * t + 1], acc.get());
+    }
+}
+
 // ---- segmented reduction of (key, point) pairs sorted by key -----------------------------------
 constexpr int SEG_BS = 128;
 
@@ -277,8 +330,8 @@ __global__ void __launch_bounds__(SEG_BS) k_seg_reduce(const uint32_t* __restric
 // One window's result is sum_j (j+1) * X[j] over its N buckets.  Thread k owns the chunk [k*m, (k+1)*m) and walks it
 // from the top with the classic running sum (2 additions per bucket):
 //     S[k] = sum X[j],      R[k] = sum (j - k*m + 1) * X[j]
-// so that   sum_j (j+1) X[j] = sum_k R[k] + m * sum_k k * S[k],   and the second term is the same problem on
-// S[1..K-1] -- the host recurses (msm.cu) and applies the powers of m = 2^mu by doublings at the very end.
+// so that   sum_j (j+1) X[j] = sum_k R[k] + m * sum_k k * S[k];   the second term goes to k_bit_sums and the host
+// applies m = 2^mu and the bit weights by doublings at the very end.
 // blockIdx.y selects the window (independent bucket arrays `strideX` apart).
 template <class F>
 __global__ void __launch_bounds__(128) k_running_sum(const XYZZ<F>* __restrict__ X, uint32_t N, uint32_t strideX, uint32_t m,
@@ -295,6 +348,28 @@ __global__ void __launch_bounds__(128) k_running_sum(const XYZZ<F>* __restrict__
     }
     st_g(&S[(size_t)blockIdx.y * K + k], acc);
     st_g(&R[(size_t)blockIdx.y * K + k], sum);
+}
+
+// k_running_sum with both accumulators in shared memory and the bucket read coordinate by coordinate from global.
+template <class F, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_running_sum_s(const XYZZ<F>* __restrict__ X, uint32_t N, uint32_t strideX, uint32_t m,
+                                                             uint32_t K, XYZZ<F>* __restrict__ S, XYZZ<F>* __restrict__ R) {
+    extern __shared__ uint4 slab[];
+    constexpr int PT = sizeof(XYZZ<F>) / 16;  // uint4 words per point
+    const SmemPoint<F, 128> acc{slab + threadIdx.x};
+    const SmemPoint<F, 128> sum{slab + PT * 128 + threadIdx.x};
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K) return;
+    const XYZZ<F>* x = X + (size_t)blockIdx.y * strideX;
+    const uint32_t lo = k * m, hi = min(N, lo + m);
+    acc.set_inf();
+    sum.set_inf();
+    for (uint32_t j = hi; j-- > lo;) {
+        pt_add_at<F>(acc, GlobalPoint<F>{x + j});
+        pt_add_at<F>(sum, acc);
+    }
+    st_g(&S[(size_t)blockIdx.y * K + k], acc.get());
+    st_g(&R[(size_t)blockIdx.y * K + k], sum.get());
 }
 
 // out[w*G + g] = sum of in[w*strideIn + i] over i = g*BS + tid, stepping by G*BS  (plain sums of the R arrays)
@@ -316,6 +391,32 @@ __global__ void __launch_bounds__(SUM_BS) k_sum_points(const XYZZ<F>* __restrict
         __syncthreads();
     }
     if (threadIdx.x == 0) st_g(&out[(size_t)blockIdx.y * gridDim.x + blockIdx.x], acc);
+}
+
+// T[bit][w][g] = sum of S[w*strideS + k] over the k in [1, K) with bit `bit` set (blockIdx.z = bit, .y = window, .x = g).
+// The j-th such k is enumerated directly, so every lane adds: k = ((j >> bit) << (bit+1)) | 1<<bit | (j & (2^bit - 1)).
+// Output index ((bit*nwin + w)*G + g): with G == 1 this is the final [bit][w] layout.
+template <class F>
+__global__ void __launch_bounds__(SUM_BS) k_bit_sums(const XYZZ<F>* __restrict__ S, uint32_t K, uint32_t strideS, XYZZ<F>* __restrict__ out) {
+    __shared__ XYZZ<F> sh[SUM_BS];
+    const uint32_t bit = blockIdx.z;
+    const XYZZ<F>* x = S + (size_t)blockIdx.y * strideS;
+    const uint32_t lowmask = (1u << bit) - 1u;
+    const uint32_t rem = K & ((2u << bit) - 1u);
+    const uint32_t count = ((K >> (bit + 1)) << bit) + (rem > (1u << bit) ? rem - (1u << bit) : 0u);
+    XYZZ<F> acc = XYZZ<F>::inf();
+    for (uint32_t j = blockIdx.x * SUM_BS + threadIdx.x; j < count; j += gridDim.x * SUM_BS) {
+        const uint32_t k = ((j >> bit) << (bit + 1)) | (1u << bit) | (j & lowmask);
+        XYZZ<F> p = ld_g(&x[k]);
+        pt_add(acc, p);
+    }
+    for (int d = SUM_BS / 2; d > 0; d >>= 1) {
+        sh[threadIdx.x] = acc;
+        __syncthreads();
+        if (threadIdx.x < d) { XYZZ<F> o = sh[threadIdx.x + d]; pt_add(acc, o); }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) st_g(&out[((size_t)bit * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x], acc);
 }
 
 // ---- precomputed window tables (resident bases only) ---------------------------------------------

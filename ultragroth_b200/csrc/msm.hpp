@@ -25,11 +25,15 @@ struct MsmConfig {
 // pre = false: per-window bucket sets (any base array); pre = true: the window size for a resident table over n bases
 MsmConfig msm_pick_config(uint64_t n, int force_c = 0, bool pre = false);
 
-// Bucket-reduction schedule (chunked running sums, msm.cuh): level l turns N[l] buckets per window into K[l] chunk sums.
+// Bucket-reduction schedule (msm.cuh): ONE level of chunked running sums turns the B buckets of a window into K chunk
+// sums S[k] and K weighted sums R[k]; the tail  sum_k k*S[k]  (k < K <= ~64Ki) is taken bit by bit:
+// T[b] = sum of S[k] over the k with bit b set -- plain, fully parallel tree sums -- and the host applies the 2^b.
+// (A recursive running sum over the chunk sums was latency-bound: every level is a serial chain of 2*2^mu additions.)
 struct MsmReducePlan {
-    int mu = 0;                      // chunk = 2^mu buckets
-    std::vector<uint32_t> N, K;      // per level
-    int levels() const { return (int)N.size(); }
+    int mu = 0;        // chunk = 2^mu buckets
+    uint32_t K = 0;    // chunk sums per window
+    int nbits = 0;     // bits of K-1 (0 when K == 1)
+    int points() const { return 1 + nbits; }  // partial sums per window handed to the host: R, T[0..nbits)
 };
 MsmReducePlan msm_reduce_plan(const MsmConfig& cfg);
 

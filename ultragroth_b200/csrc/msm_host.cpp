@@ -10,20 +10,22 @@ template <class HF>
 static void msm_finish_impl(DeviceCtx& ctx, const MsmDigits& dg, const std::string& slot, XYZZ<HF>* out) {
     ctx.wait("msm." + slot);
     const MsmReducePlan plan = msm_reduce_plan(dg.cfg);
-    const int nwin = dg.cfg.nwin(), L = plan.levels();
+    const int nwin = dg.cfg.nwin(), L = plan.points();
     const XYZZ<HF>* U = (const XYZZ<HF>*)ctx.pinned("msm.sums." + slot, (size_t)64 * 32 * sizeof(XYZZ<HF>) + 16);
     uint32_t entries = 0;
     memcpy(&entries, (const uint8_t*)U + (size_t)L * nwin * sizeof(XYZZ<HF>), 4);
     if (ctx.profile) ctx.counters[sizeof(HF) == 32 ? "#msm_entries<G1>" : "#msm_entries<G2>"] += entries;
-    // window w: sum_l 2^(mu*l) * U[l][w]; windows: sum_w 2^(c*w) * (...), both by Horner
+    // window w: U[0][w] + 2^mu * sum_b 2^b * U[1+b][w]; windows: sum_w 2^(c*w) * (...), both by Horner
     XYZZ<HF> acc = XYZZ<HF>::inf();
     for (int w = nwin - 1; w >= 0; w--) {
         for (int k = 0; k < dg.cfg.c; k++) acc = pt_dbl(acc);
         XYZZ<HF> win = XYZZ<HF>::inf();
-        for (int l = L - 1; l >= 0; l--) {
-            for (int k = 0; k < plan.mu; k++) win = pt_dbl(win);
-            pt_add(win, U[(size_t)l * nwin + w]);
+        for (int b = plan.nbits - 1; b >= 0; b--) {
+            win = pt_dbl(win);
+            pt_add(win, U[(size_t)(1 + b) * nwin + w]);
         }
+        for (int k = 0; k < plan.mu; k++) win = pt_dbl(win);
+        pt_add(win, U[(size_t)w]);
         pt_add(acc, win);
     }
     *out = acc;
