@@ -32,6 +32,8 @@ def parse():
     ap.add_argument("--cpu-logn", type=int, default=int(os.environ.get("UGB_BENCH_CPU_LOGN", "16")))
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-verify", action="store_true")
+    ap.add_argument("--shard", action="store_true",
+                    help="one proof at a time over ALL ranks: MSMs sharded by point range (SURVEY 8(e)) instead of replicas")
     return ap.parse_args()
 
 
@@ -129,6 +131,8 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    if args.shard:
+        return main_sharded(args, torch, dist, world, rank, local)
     ctx = ug.Context(local)
     ultra = args.workload == "ultragroth"
     lookup_bits, chunks = lookup_params(args.logn)
@@ -257,6 +261,80 @@ def main():
                 line["cpu_baseline"] = {"error": str(e)[:200]}
         print(json.dumps(line), flush=True)
     prover.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main_sharded(args, torch, dist, world, rank, local):
+    """Single-proof latency with the MSMs sharded by point range over all ranks (strong scaling): every rank keeps 1/N of
+    each base array resident, the H pipeline is replicated, one all-gather of the partial sums per phase, rank 0 assembles."""
+    import secrets
+    import ultragroth_b200 as ug
+    from ultragroth_b200 import sharded
+    from oracle import groth16 as og
+    ctx = ug.Context(local)
+    ultra = args.workload == "ultragroth"
+    lookup_bits, chunks = lookup_params(args.logn)
+    t_setup = time.time()
+    zkey, wtns, vkj = ctx.synth(args.logn, seed=0xB200 + args.logn, ultra=ultra, lookup_bits=lookup_bits, n_chunks=chunks)
+    t_setup = time.time() - t_setup
+    t_create = time.time()
+    sp = sharded.ShardedProver(zkey, "ultragroth" if ultra else "groth16", rank=rank, world=world)
+    t_create = time.time() - t_create
+    zkey_bytes = int(zkey.nbytes)
+    del zkey
+    wt = torch.from_numpy(wtns).pin_memory().numpy()
+    rk = (1 << 200) + 0xB200  # common r_k for UltraGroth (any value < 2^248; fixed so that every rank agrees)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    res = None
+    for _ in range(max(args.warmup, 3)):
+        res = sp.prove(wt, rk=rk if ultra else None)
+    verified = None
+    if rank == 0 and not args.no_verify:
+        proof = og.proof_from_json(res[0])
+        public = [int(x) for x in json.loads(res[1])] if res[1] != "null" else []
+        verified = bool(og.ultragroth_verify(og.vk_from_ultragroth_json(vkj), proof, public) if ultra
+                        else og.groth16_verify(og.vk_from_snarkjs_json(vkj), proof, public))
+        if not verified:
+            raise SystemExit("bench: the sharded proof does not verify -- refusing to report a number")
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.perf_counter()
+    ev0.record()
+    for _ in range(args.steps):
+        sp.prove(wt, rk=rk if ultra else None)
+    ev1.record()
+    barrier()
+    t = max(time.perf_counter() - t0, ev0.elapsed_time(ev1) * 1e-3)
+    sampler.stop_flag.set()
+    sampler.join(timeout=2)
+    if world > 1:
+        tt = torch.tensor([t], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t = float(tt[0])
+    if rank == 0:
+        nvars = int.from_bytes(wtns[60:64].tobytes(), "little")
+        line = {"metric": "proofs_per_sec", "value": args.steps / t, "unit": "proofs/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": 1000.0 * t / args.steps, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "u256 (8x32-bit Montgomery limbs, BN254 Fr/Fq)", "data": "synthetic",
+                "config": {"workload": workload_name(args), "nVars": nvars, "domainSize": 1 << args.logn,
+                           "parallelism": f"msm point-range shard x{world} (H pipeline replicated)",
+                           "l2": "inputs exceed L2 (zkey bases %.2f GB over %d GPUs)" % (zkey_bytes / 1e9, world)},
+                "e2e": {"value": args.steps / t, "unit": "proofs/s", "ms_per_proof": 1000.0 * t / args.steps,
+                        "h2d_bytes_per_step": int(wtns.nbytes), "d2h_bytes_per_step": int(sp.partial_size),
+                        "api": "ugb_*_prove_partial + all_gather + ugb_*_prove_assemble"},
+                "gpu_launches": None, "clocks": sampler.summary(), "verified": verified,
+                "setup_s": round(t_setup, 2), "create_s": round(t_create, 2)}
+        print(json.dumps(line), flush=True)
+    sp.close()
     if world > 1:
         dist.destroy_process_group()
 

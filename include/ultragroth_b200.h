@@ -104,6 +104,31 @@ int ugb_prover_set_profile(void* prover_object, int enable);
 uint64_t ugb_prover_kernel_stats(void* prover_object, char* out, uint64_t cap);
 void* ugb_prover_stream(void* prover_object);
 
+/* ---- point-range sharded proving ("MSMs shard by point range across GPUs, partial sums reduced
+ * on the host or via NCCL") ----
+ * One prover object per GPU / process keeps slice `rank` of `world` of every zkey base array resident (A, B1, B2, C,
+ * H, UltraGroth's round C); witness, coefficients and the H pipeline are replicated.  The MSM partial sums are opaque
+ * host blobs of ugb_prover_partial_size() bytes; the caller exchanges them (one all-gather) and any rank assembles.
+ * They replace, per shard, the MSM calls of src/groth16.cpp:53-64,153-154 / src/ultra_groth.cpp:168,203-234,329; the
+ * assemble calls are src/groth16.cpp:158-250 / src/ultra_groth.cpp:337-399,476-513.  Return codes as include/prover.h. */
+uint64_t ugb_prover_partial_size(void);
+int ugb_prover_create_sharded(void** prover_object, const void* zkey_buffer, unsigned long long zkey_size, int ultra, uint32_t rank,
+                              uint32_t world, char* error_msg, unsigned long long error_msg_maxsize);
+int ugb_groth16_prove_partial(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, void* partial_out,
+                              char* error_msg, unsigned long long error_msg_maxsize);
+int ugb_groth16_prove_assemble(void* prover_object, const void* partials, uint32_t count, const void* wtns_buffer,
+                               unsigned long long wtns_size, char* proof_buffer, unsigned long long* proof_size, char* public_buffer,
+                               unsigned long long* public_size, char* error_msg, unsigned long long error_msg_maxsize);
+/* UltraGroth: round partial (128 bytes) -> exchange -> final partial (needs ALL round partials and the common r_k) ->
+ * exchange -> assemble.  rk32: 32-byte little-endian raw scalar, identical on every shard. */
+int ugb_ultra_round_partial(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, void* round_partial_out,
+                            char* error_msg, unsigned long long error_msg_maxsize);
+int ugb_ultra_final_partial(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, const void* round_partials,
+                            uint32_t count, const void* rk32, void* partial_out, char* error_msg, unsigned long long error_msg_maxsize);
+int ugb_ultra_prove_assemble(void* prover_object, const void* partials, uint32_t count, const void* rk32, char* proof_buffer,
+                             unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
+                             unsigned long long error_msg_maxsize);
+
 /* ---- microbenchmarks for the roofline denominators ----
  * kind 0: independent 32-bit IMAD chains; 1: IMAD.WIDE (mad.wide.u32) chains; 2: dependent Fq Montgomery
  * products (4 chains per thread).  Returns operations per second in *ops_per_s. */

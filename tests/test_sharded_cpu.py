@@ -11,6 +11,13 @@ from ultragroth_b200 import sharded
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
+def _free_port():
+    import socket
+    with socket.socket() as so:
+        so.bind(("127.0.0.1", 0))
+        return so.getsockname()[1]
+
+
 WORKER = r'''
 import os, sys
 sys.path.insert(0, os.environ["UGB_ROOT"])
@@ -65,7 +72,7 @@ def test_world2_gloo_sharded_msm(tmp_path):
     script.write_text(WORKER)
     env = dict(os.environ, UGB_ROOT=ROOT, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="1")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-           "--master-port", "29533", str(script)]
+           "--master-port", str(_free_port()), str(script)]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert "ok 0" in res.stdout and "ok 1" in res.stdout

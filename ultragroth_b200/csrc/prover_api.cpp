@@ -179,7 +179,7 @@ int pick_device() {
 
 class ProverBase {
 public:
-    ProverBase(const void* zkey_buffer, unsigned long long zkey_size, bool ultra)
+    ProverBase(const void* zkey_buffer, unsigned long long zkey_size, bool ultra, uint32_t shard_rank = 0, uint32_t shard_world = 1)
         : zkey(zkey_buffer, zkey_size, "zkey", 1), hdr(load_zkey_header(zkey, ultra)) {
         if (!prime_is_bn254_r(hdr.rPrime, hdr.n8r)) throw std::invalid_argument("zkey curve not supported");
         // the header points (alpha, beta, delta...) are copied: the zkey buffer is only borrowed during create
@@ -187,7 +187,7 @@ public:
         hdr_copy.assign(zkey.data(2), zkey.data(2) + zkey.size(2));
         BinFile::Section s{hdr_copy.data(), hdr_copy.size()};
         rebase(s);
-        dev.reset(new ProverDevice(pick_device(), zkey, hdr));
+        dev.reset(new ProverDevice(pick_device(), zkey, hdr, shard_rank, shard_world));
     }
     virtual ~ProverBase() {}
 
@@ -207,11 +207,23 @@ protected:
     }
 };
 
+// sum of per-shard partial MSM results (point-range sharding: every shard returns its slice's XYZZ sums)
+static ProofMsms sum_partials(const ProofMsms* parts, uint32_t count) {
+    if (count == 0) throw std::invalid_argument("no partial sums");
+    ProofMsms m = parts[0];
+    for (uint32_t i = 1; i < count; i++) {
+        pt_add(m.a, parts[i].a); pt_add(m.b1, parts[i].b1); pt_add(m.c, parts[i].c); pt_add(m.h, parts[i].h);
+        pt_add(m.b2, parts[i].b2);
+    }
+    return m;
+}
+
 class Groth16Prover : public ProverBase {
 public:
-    Groth16Prover(const void* zkey_buffer, unsigned long long zkey_size) : ProverBase(zkey_buffer, zkey_size, false) {}
+    Groth16Prover(const void* zkey_buffer, unsigned long long zkey_size, uint32_t shard_rank = 0, uint32_t shard_world = 1)
+        : ProverBase(zkey_buffer, zkey_size, false, shard_rank, shard_world) {}
 
-    void prove(const void* wtns_buffer, unsigned long long wtns_size, std::string& stringProof, std::string& stringPublic) {
+    const uint8_t* check_witness(const void* wtns_buffer, unsigned long long wtns_size) {
         BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
         WtnsHeader wh = load_wtns_header(wtns);
         if (hdr.nVars != wh.nVars)
@@ -219,9 +231,14 @@ public:
                                                 ", witness: " + std::to_string(wh.nVars));
         if (!prime_is_bn254_r(wh.prime, wh.n8)) throw std::invalid_argument("different wtns curve");
         if (wtns.size(2) < (uint64_t)hdr.nVars * 32) throw std::range_error("wtns section too short: signals");
-        const uint8_t* w = wtns.data(2);
-        ProofMsms m;
-        dev->prove_groth16(w, m);
+        return wtns.data(2);
+    }
+    // device half: the five MSMs over this prover's point range (the whole range when not sharded)
+    void msms(const void* wtns_buffer, unsigned long long wtns_size, ProofMsms& m) {
+        dev->prove_groth16(check_witness(wtns_buffer, wtns_size), m);
+    }
+    // host half: blinding, assembly, JSON (src/groth16.cpp:158-250)
+    void finish(const ProofMsms& m, const uint8_t* w, std::string& stringProof, std::string& stringPublic) {
         Scalar r = blinding.fixed ? blinding.r : random_blinding();
         Scalar s = blinding.fixed ? blinding.s : random_blinding();
         HG1Affine A, C;
@@ -230,16 +247,24 @@ public:
         stringProof = "{\"pi_a\":" + g1_json(A) + ",\"pi_b\":" + g2_json(B) + ",\"pi_c\":" + g1_json(C) + ",\"protocol\":\"groth16\"}";
         stringPublic = public_json(w + 32, hdr.nPublic, 0);
     }
+    void prove(const void* wtns_buffer, unsigned long long wtns_size, std::string& stringProof, std::string& stringPublic) {
+        const uint8_t* w = check_witness(wtns_buffer, wtns_size);
+        ProofMsms m;
+        dev->prove_groth16(w, m);
+        finish(m, w, stringProof, stringPublic);
+    }
     unsigned long long proofBufferMinSize() const { return ProofBufferMinSize(); }
     unsigned long long publicBufferMinSize() const { return PublicBufferMinSize(hdr.nPublic); }
 };
 
 class UltraGrothProver : public ProverBase {
 public:
-    UltraGrothProver(const void* zkey_buffer, unsigned long long zkey_size) : ProverBase(zkey_buffer, zkey_size, true) {}
+    UltraGrothProver(const void* zkey_buffer, unsigned long long zkey_size, uint32_t shard_rank = 0, uint32_t shard_world = 1)
+        : ProverBase(zkey_buffer, zkey_size, true, shard_rank, shard_world) {}
 
-    void prove(const void* wtns_buffer, unsigned long long wtns_size, std::string& stringProof, std::string& stringPublic) {
-        BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
+    struct Lookup { std::vector<uint32_t> chunks, freqs, widx, pidx; };
+
+    const uint8_t* check_witness(const BinFile& wtns, Lookup& lk) {
         WtnsHeader wh = load_wtns_header(wtns);
         if (hdr.nVars != wh.nVars)
             throw InvalidWitnessLengthException("Invalid witness length. Circuit: " + std::to_string(hdr.nVars) +
@@ -252,26 +277,30 @@ public:
             v.resize(cnt);
             if (cnt) memcpy(v.data(), wtns.data(id), cnt * 4);
         };
-        std::vector<uint32_t> chunks, freqs, widx, pidx;
-        u32s(3, chunks); u32s(4, freqs); u32s(5, widx); u32s(6, pidx);
-        if (widx.size() != pidx.size()) {
+        u32s(3, lk.chunks); u32s(4, lk.freqs); u32s(5, lk.widx); u32s(6, lk.pidx);
+        if (lk.widx.size() != lk.pidx.size()) {
             // the reference iterates wtns_indxs_len entries of both arrays
-            if (pidx.size() < widx.size()) throw std::range_error("wtns push index section shorter than witness index section");
+            if (lk.pidx.size() < lk.widx.size()) throw std::range_error("wtns push index section shorter than witness index section");
         }
-        dev->ultra_upload_witness(wtns.data(2));
-        // round 1: commitment = MSM(round_pointsC, round_wtns) + r_k * final_delta1 (src/ultra_groth.cpp:161-184)
-        HG1XYZZ commit;
-        dev->ultra_round_msm(commit);
-        Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
+        return wtns.data(2);
+    }
+    // round 1, device half: upload + MSM(round_pointsC, round_wtns) over this prover's point range
+    void round_msm(const uint8_t* w, HG1XYZZ& partial) {
+        dev->ultra_upload_witness(w);
+        dev->ultra_round_msm(partial);
+    }
+    // commitment = (sum of the round MSM) + r_k * final_delta1 (src/ultra_groth.cpp:161-184), then the challenge,
+    // the lookup fill and the final-round MSMs over this prover's point range
+    void final_msms(HG1XYZZ commit, const Scalar& rk, const Lookup& lk, HG1Affine& commit_aff, ProofMsms& m) {
         HG1XYZZ fdelta1 = from_affine_bytes<HFq>(hdr.final_delta1);
         pt_add(commit, pt_mul(fdelta1, rk));
-        HG1Affine commit_aff = pt_to_affine(commit);
-        // derive_challenge (src/ultra_groth.cpp:32-58)
-        HFr rand_mont = derive_challenge(commit_aff);
-        dev->ultra_lookup(chunks.data(), (uint32_t)chunks.size(), freqs.data(), (uint32_t)freqs.size(), widx.data(), pidx.data(),
-                          (uint32_t)widx.size(), rand_mont);
-        ProofMsms m;
+        commit_aff = pt_to_affine(commit);
+        HFr rand_mont = derive_challenge(commit_aff);  // src/ultra_groth.cpp:32-58
+        dev->ultra_lookup(lk.chunks.data(), (uint32_t)lk.chunks.size(), lk.freqs.data(), (uint32_t)lk.freqs.size(), lk.widx.data(),
+                          lk.pidx.data(), (uint32_t)lk.widx.size(), rand_mont);
         dev->ultra_final_msms(m);
+    }
+    void finish(const ProofMsms& m, const Scalar& rk, const HG1Affine& commit_aff, std::string& stringProof, std::string& stringPublic) {
         Scalar r = blinding.fixed ? blinding.r : random_blinding();
         Scalar s = blinding.fixed ? blinding.s : random_blinding();
         HG1Affine A, C;
@@ -282,6 +311,18 @@ public:
         std::vector<uint8_t> pub((size_t)hdr.nPublic * 32);
         if (hdr.nPublic) dev->download_witness(pub.data(), 1, hdr.nPublic);
         stringPublic = public_json(pub.data(), hdr.nPublic, hdr.rand_indx);
+    }
+    void prove(const void* wtns_buffer, unsigned long long wtns_size, std::string& stringProof, std::string& stringPublic) {
+        BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
+        Lookup lk;
+        const uint8_t* w = check_witness(wtns, lk);
+        HG1XYZZ commit;
+        round_msm(w, commit);
+        Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
+        HG1Affine commit_aff;
+        ProofMsms m;
+        final_msms(commit, rk, lk, commit_aff, m);
+        finish(m, rk, commit_aff, stringProof, stringPublic);
     }
     unsigned long long proofBufferMinSize() const { return ProofBufferMinSizeUltraGroth(); }
     unsigned long long publicBufferMinSize() const { return PublicBufferMinSize((unsigned long long)hdr.nPublic - 1); }
@@ -553,6 +594,123 @@ uint64_t ugb_prover_kernel_launches(void* prover_object) {
 void* ugb_prover_stream(void* prover_object) {
     if (!prover_object) return nullptr;
     return (void*)static_cast<ProverBase*>(prover_object)->dev->ctx().stream;
+}
+
+
+// ---- point-range sharded proving (declared in include/ultragroth_b200.h) ---------
+// One prover object per GPU/process holds slice `rank` of `world` of every base array.  The MSM partial sums are
+// plain host structs (ugb_prover_partial_size() bytes) that the caller exchanges (NCCL / gloo all-gather, or a
+// host gather) and hands back to *_assemble on the rank that emits the proof.
+uint64_t ugb_prover_partial_size(void) { return sizeof(ProofMsms); }
+
+int ugb_prover_create_sharded(void** prover_object, const void* zkey_buffer, unsigned long long zkey_size, int ultra, uint32_t rank,
+                              uint32_t world, char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (prover_object == NULL) throw std::invalid_argument("Null prover object");
+    if (zkey_buffer == NULL) throw std::invalid_argument("Null zkey buffer");
+    if (ultra) *prover_object = static_cast<ProverBase*>(new UltraGrothProver(zkey_buffer, zkey_size, rank, world));
+    else *prover_object = static_cast<ProverBase*>(new Groth16Prover(zkey_buffer, zkey_size, rank, world));
+    API_CATCH_CREATE
+}
+
+int ugb_groth16_prove_partial(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, void* partial_out,
+                              char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !wtns_buffer || !partial_out) throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    if (b->is_ultra()) throw std::invalid_argument("not a groth16 prover");
+    ProofMsms m;
+    static_cast<Groth16Prover*>(b)->msms(wtns_buffer, wtns_size, m);
+    memcpy(partial_out, &m, sizeof(m));
+    API_CATCH_PROVE
+}
+
+int ugb_groth16_prove_assemble(void* prover_object, const void* partials, uint32_t count, const void* wtns_buffer,
+                               unsigned long long wtns_size, char* proof_buffer, unsigned long long* proof_size, char* public_buffer,
+                               unsigned long long* public_size, char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !partials || !wtns_buffer || !proof_buffer || !proof_size || !public_buffer || !public_size)
+        throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    if (b->is_ultra()) throw std::invalid_argument("not a groth16 prover");
+    Groth16Prover* prover = static_cast<Groth16Prover*>(b);
+    CheckAndUpdateBufferSizes(prover->proofBufferMinSize(), proof_size, prover->publicBufferMinSize(), public_size, "Minimum");
+    std::vector<ProofMsms> parts(count);
+    memcpy(parts.data(), partials, (size_t)count * sizeof(ProofMsms));
+    ProofMsms m = sum_partials(parts.data(), count);
+    std::string stringProof, stringPublic;
+    prover->finish(m, prover->check_witness(wtns_buffer, wtns_size), stringProof, stringPublic);
+    CheckAndUpdateBufferSizes(stringProof.length(), proof_size, stringPublic.length(), public_size, "Required");
+    std::strncpy(proof_buffer, stringProof.c_str(), *proof_size);
+    std::strncpy(public_buffer, stringPublic.c_str(), *public_size);
+    API_CATCH_PROVE
+}
+
+// UltraGroth, phase 1: witness upload + this shard's part of the round commitment MSM (128-byte XYZZ)
+int ugb_ultra_round_partial(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, void* round_partial_out,
+                            char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !wtns_buffer || !round_partial_out) throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    if (!b->is_ultra()) throw std::invalid_argument("not an ultragroth prover");
+    UltraGrothProver* prover = static_cast<UltraGrothProver*>(b);
+    BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
+    UltraGrothProver::Lookup lk;
+    const uint8_t* w = prover->check_witness(wtns, lk);
+    HG1XYZZ part;
+    prover->round_msm(w, part);
+    memcpy(round_partial_out, &part, sizeof(part));
+    API_CATCH_PROVE
+}
+
+// phase 2: every shard sums ALL round partials, adds r_k * delta (rk32: the SAME 32-byte scalar on every shard), derives
+// the challenge, fills the lookup signals in its witness copy and runs the final-round MSMs over its point range.
+int ugb_ultra_final_partial(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, const void* round_partials,
+                            uint32_t count, const void* rk32, void* partial_out, char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !wtns_buffer || !round_partials || !rk32 || !partial_out || count == 0) throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    if (!b->is_ultra()) throw std::invalid_argument("not an ultragroth prover");
+    UltraGrothProver* prover = static_cast<UltraGrothProver*>(b);
+    BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
+    UltraGrothProver::Lookup lk;
+    prover->check_witness(wtns, lk);
+    std::vector<HG1XYZZ> rp(count);
+    memcpy(rp.data(), round_partials, (size_t)count * sizeof(HG1XYZZ));
+    HG1XYZZ commit = rp[0];
+    for (uint32_t i = 1; i < count; i++) pt_add(commit, rp[i]);
+    Scalar rk;
+    memcpy(&rk, rk32, 32);
+    HG1Affine commit_aff;
+    ProofMsms m;
+    prover->final_msms(commit, rk, lk, commit_aff, m);
+    m.round_c = XYZZ<HFq>::from_affine(commit_aff);  // the blinded commitment, identical on every shard
+    memcpy(partial_out, &m, sizeof(m));
+    API_CATCH_PROVE
+}
+
+int ugb_ultra_prove_assemble(void* prover_object, const void* partials, uint32_t count, const void* rk32, char* proof_buffer,
+                             unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
+                             unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !partials || !rk32 || !proof_buffer || !proof_size || !public_buffer || !public_size || count == 0)
+        throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    if (!b->is_ultra()) throw std::invalid_argument("not an ultragroth prover");
+    UltraGrothProver* prover = static_cast<UltraGrothProver*>(b);
+    CheckAndUpdateBufferSizes(prover->proofBufferMinSize(), proof_size, prover->publicBufferMinSize(), public_size, "Minimum");
+    std::vector<ProofMsms> parts(count);
+    memcpy(parts.data(), partials, (size_t)count * sizeof(ProofMsms));
+    ProofMsms m = sum_partials(parts.data(), count);
+    Scalar rk;
+    memcpy(&rk, rk32, 32);
+    HG1Affine commit_aff = pt_to_affine(parts[0].round_c);
+    std::string stringProof, stringPublic;
+    prover->finish(m, rk, commit_aff, stringProof, stringPublic);
+    CheckAndUpdateBufferSizes(stringProof.length(), proof_size, stringPublic.length(), public_size, "Required");
+    std::strncpy(proof_buffer, stringProof.c_str(), *proof_size);
+    std::strncpy(public_buffer, stringPublic.c_str(), *public_size);
+    API_CATCH_PROVE
 }
 
 }  // extern "C"

@@ -165,8 +165,12 @@ static int ilog2_exact(uint32_t n) {
     return k;
 }
 
-ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
+ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h, uint32_t shard_rank, uint32_t shard_world)
     : nVars(h.nVars), nPublic(h.nPublic), domainSize(h.domainSize), ultra_(h.ultra) {
+    if (shard_world == 0 || shard_rank >= shard_world) throw std::invalid_argument("bad shard rank / world");
+    shard_range(nVars, shard_world, shard_rank, w_lo_, w_hi_);
+    shard_range(domainSize, shard_world, shard_rank, h_lo_, h_hi_);
+    const uint64_t wn = w_hi_ - w_lo_, hn = h_hi_ - h_lo_;
     if (h.n8q != 32 || h.n8r != 32) throw std::invalid_argument("zkey field size not supported");
     logn = ilog2_exact(domainSize);
     if (nPublic + 1 > nVars) throw std::invalid_argument("zkey header is inconsistent (nPublic >= nVars)");
@@ -182,9 +186,9 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
     need(5, (uint64_t)nVars * 64, "pointsA");
     need(6, (uint64_t)nVars * 64, "pointsB1");
     need(7, (uint64_t)nVars * 128, "pointsB2");
-    A_ = upload(ctx, zkey.data(5), (size_t)nVars * 64);
-    B1_ = upload(ctx, zkey.data(6), (size_t)nVars * 64);
-    B2_ = upload(ctx, zkey.data(7), (size_t)nVars * 128);
+    A_ = upload(ctx, zkey.data(5) + w_lo_ * 64, (size_t)wn * 64);
+    B1_ = upload(ctx, zkey.data(6) + w_lo_ * 64, (size_t)wn * 64);
+    B2_ = upload(ctx, zkey.data(7) + w_lo_ * 128, (size_t)wn * 128);
     std::vector<uint8_t> cfull;  // must outlive the async copy
     if (!ultra_) {
         const uint32_t nc = nVars - nPublic - 1;
@@ -192,11 +196,16 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
         need(9, (uint64_t)domainSize * 64, "pointsH");
         // C pairs with witness[nPublic+1 ..] (src/groth16.cpp:64): pad with points at infinity so that the
         // C MSM reuses the sorted digits of the full witness
-        C_ = dev_alloc((size_t)nVars * 64);
-        UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, (size_t)(nPublic + 1) * 64, ctx.stream));
-        if (nc) UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)C_ + (size_t)(nPublic + 1) * 64, zkey.data(8), (size_t)nc * 64, cudaMemcpyHostToDevice, ctx.stream));
+        // slot i of the padded array = pointsC[i - (nPublic+1)] for i > nPublic, infinity below; keep [w_lo_, w_hi_)
+        C_ = dev_alloc((size_t)wn * 64);
+        UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, std::max<size_t>((size_t)wn * 64, 16), ctx.stream));
+        {
+            const uint64_t first = std::max<uint64_t>(w_lo_, (uint64_t)nPublic + 1);
+            if (first < w_hi_)
+                UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)C_ + (first - w_lo_) * 64, zkey.data(8) + (first - nPublic - 1) * 64, (size_t)(w_hi_ - first) * 64, cudaMemcpyHostToDevice, ctx.stream));
+        }
         c_shares_witness_sort_ = true;
-        H_ = upload(ctx, zkey.data(9), (size_t)domainSize * 64);
+        H_ = upload(ctx, zkey.data(9) + h_lo_ * 64, (size_t)hn * 64);
     } else {
         n_c1_ = h.num_indexes_c1;
         n_c2_ = h.num_indexes_c2;
@@ -218,7 +227,8 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
                 seen[v] = true;
             }
         }
-        C1_ = upload(ctx, zkey.data(8), (size_t)n_c1_ * 64);
+        shard_range(n_c1_, shard_world, shard_rank, c1_lo_, c1_hi_);
+        C1_ = upload(ctx, zkey.data(8) + c1_lo_ * 64, (size_t)(c1_hi_ - c1_lo_) * 64);
         idx_c1_ = (uint32_t*)upload(ctx, zkey.data(10), (size_t)n_c1_ * 4);
         idx_c2_ = (uint32_t*)upload(ctx, zkey.data(11), (size_t)n_c2_ * 4);
         if (unique) {
@@ -227,13 +237,14 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
             cfull.assign((size_t)nVars * 64, 0);
             const uint8_t* c2 = zkey.data(9);
             for (uint32_t i = 0; i < n_c2_; i++) { uint32_t v; memcpy(&v, i2 + i, 4); memcpy(&cfull[(size_t)v * 64], c2 + (size_t)i * 64, 64); }
-            C_ = upload(ctx, cfull.data(), cfull.size());
+            C_ = upload(ctx, cfull.data() + w_lo_ * 64, (size_t)wn * 64);
             c_shares_witness_sort_ = true;
         } else {
+            if (shard_world > 1) throw std::invalid_argument("sharded UltraGroth prover needs unique final-round indexes");
             C_ = upload(ctx, zkey.data(9), (size_t)n_c2_ * 64);
             c_shares_witness_sort_ = false;
         }
-        H_ = upload(ctx, zkey.data(12), (size_t)domainSize * 64);
+        H_ = upload(ctx, zkey.data(12) + h_lo_ * 64, (size_t)hn * 64);
     }
 
     // coefficient records {u32 m, u32 c, u32 s, Fr coef} packed(1) after a u32 count (src/groth16.cpp:38,
@@ -301,13 +312,13 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h)
                 cfg = t.cfg;
             };
             MsmConfig tmp;
-            tabulate(A_, 1, nVars, cfg_w_);
-            tabulate(B1_, 1, nVars, tmp);
-            tabulate(B2_, 2, nVars, tmp);
-            if (c_shares_witness_sort_) tabulate(C_, 1, nVars, tmp);
+            tabulate(A_, 1, wn, cfg_w_);
+            tabulate(B1_, 1, wn, tmp);
+            tabulate(B2_, 2, wn, tmp);
+            if (c_shares_witness_sort_) tabulate(C_, 1, wn, tmp);
             else tabulate(C_, 1, n_c2_, cfg_c2_);
-            tabulate(H_, 1, domainSize, cfg_h_);
-            if (ultra_) tabulate(C1_, 1, n_c1_, cfg_c1_);
+            tabulate(H_, 1, hn, cfg_h_);
+            if (ultra_) tabulate(C1_, 1, c1_hi_ - c1_lo_, cfg_c1_);
         }
     }
     w_ = dev_alloc((size_t)nVars * 32);
@@ -356,7 +367,7 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     mark();  // 0
     // the four witness MSMs share one digit sort (src/groth16.cpp:53-64 all read the same scalars)
     MsmDigits dw;
-    msm_sort_digits(ctx, (const uint8_t*)w_, nullptr, nVars, 0, "w", dw, pre_ ? &cfg_w_ : nullptr);
+    msm_sort_digits(ctx, (const uint8_t*)w_ + w_lo_ * 32, nullptr, w_hi_ - w_lo_, 0, "w", dw, pre_ ? &cfg_w_ : nullptr);
     mark();  // 1
     msm_g1_launch(ctx, A_, dw, "a");
     mark();  // 2
@@ -390,7 +401,7 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     UG_KERNEL(ctx, "k_h_final", k_h_final<<<blocks, 256, 0, ctx.stream>>>((Fr*)a_, (const Fr*)b_, (const Fr*)c_, n));
     mark();  // 9
     MsmDigits dh;
-    msm_sort_digits(ctx, (const uint8_t*)a_, nullptr, n, 0, "h", dh, pre_ ? &cfg_h_ : nullptr);
+    msm_sort_digits(ctx, (const uint8_t*)a_ + h_lo_ * 32, nullptr, h_hi_ - h_lo_, 0, "h", dh, pre_ ? &cfg_h_ : nullptr);
     mark();  // 10
     msm_g1_launch(ctx, H_, dh, "h");
     mark();  // 11
@@ -432,7 +443,7 @@ void ProverDevice::ultra_round_msm(HG1XYZZ& out) {
     ctx.activate();
     // round_wtns[i] = wtns[round_indexes[i]] (src/ultra_groth.cpp:415-419) folded into the scalar fetch
     MsmDigits d;
-    msm_sort_digits(ctx, (const uint8_t*)w_, idx_c1_, n_c1_, 0, "round", d, pre_ ? &cfg_c1_ : nullptr);
+    msm_sort_digits(ctx, (const uint8_t*)w_, idx_c1_ + c1_lo_, c1_hi_ - c1_lo_, 0, "round", d, pre_ ? &cfg_c1_ : nullptr);
     msm_g1_launch(ctx, C1_, d, "round");
     msm_g1_finish(ctx, d, "round", &out);
 }

@@ -2,6 +2,7 @@
 // pointers (src/groth16.hpp:74-114, src/ultra_groth.hpp:108-206) lives here in HBM instead, uploaded
 // once at *_prover_create (north star item 4: bases and twiddles stay resident across proofs).
 #pragma once
+#include <algorithm>
 #include <memory>
 #include <string>
 #include <vector>
@@ -27,8 +28,15 @@ struct StageTimes {  // milliseconds of device time per stage of the last proof 
 
 class ProverDevice {
 public:
-    // point range [lo, hi) of every base array kept by this device; full = does the H pipeline
-    ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& hdr);
+    // shard_rank / shard_world: point-range sharding: this device keeps only slice
+    // shard_range(count, world, rank) of every base array resident and its MSMs return PARTIAL sums; the
+    // witness, the coefficients and the H pipeline are replicated on every shard.
+    ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& hdr, uint32_t shard_rank = 0, uint32_t shard_world = 1);
+    static void shard_range(uint64_t n, uint32_t world, uint32_t rank, uint64_t& lo, uint64_t& hi) {
+        const uint64_t base = n / world, rem = n % world;
+        lo = rank * base + std::min<uint64_t>(rank, rem);
+        hi = lo + base + (rank < rem ? 1 : 0);
+    }
     ~ProverDevice();
 
     DeviceCtx& ctx() { return *ctx_; }
@@ -63,6 +71,8 @@ private:
     std::unique_ptr<NttTables> tabs_;
     bool ultra_;
     uint32_t n_c1_ = 0, n_c2_ = 0;
+    // resident slices: witness-paired arrays hold points [w_lo_, w_hi_), H holds [h_lo_, h_hi_), C1 [c1_lo_, c1_hi_)
+    uint64_t w_lo_ = 0, w_hi_ = 0, h_lo_ = 0, h_hi_ = 0, c1_lo_ = 0, c1_hi_ = 0;
     // bases
     void *A_ = nullptr, *B1_ = nullptr, *B2_ = nullptr, *C_ = nullptr, *H_ = nullptr, *C1_ = nullptr;
     bool c_shares_witness_sort_ = false;
