@@ -11,10 +11,10 @@ except Exception as e:
     print("$name FAILED", e, open("gpurun_out/v_$name.err").read()[-300:])
 PY
 }
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-run base X=1
-run rsg2_0 UGB_RS_G2=0
-run rsg2_13 UGB_RS_G2=13
-run rsg1_13 UGB_RS_G1=13
-run rsg1_3 UGB_RS_G1=3
-run rsg1_4 UGB_RS_G1=4
+UGB_ACC_G1=23 UGB_ACC_G2=32 timeout 600 python -m pytest tests/test_gpu_msm.py tests/test_gpu_prover.py tests/test_gpu_synth.py -m gpu -x -q 2>&1 | tail -4
+run ba_g1_22 UGB_ACC_G1=22
+run ba_g1_23 UGB_ACC_G1=23
+run ba_g1_24 UGB_ACC_G1=24
+run ba_g1_33 UGB_ACC_G1=33
+run ba_g2_32 UGB_ACC_G2=32
+run ba_g2_33 UGB_ACC_G2=33

@@ -79,6 +79,7 @@ __device__ __forceinline__ Fqc fadd(const Fqc& x, const Fqc& y) { return fp_add(
 __device__ __forceinline__ Fqc fsub(const Fqc& x, const Fqc& y) { return fp_sub(x, y); }
 __device__ __forceinline__ Fqc fneg(const Fqc& x) { return fp_neg(x); }
 __device__ __forceinline__ Fqc fdbl(const Fqc& x) { return fp_add(x, x); }
+__device__ __forceinline__ Fqc finv(const Fqc& x) { return fp_inv(x); }
 __device__ __forceinline__ Fqc fmul(const Fqc& x, const Fqc& y) { return fqc_mul_call(x, y); }
 __device__ __forceinline__ Fqc fsqr(const Fqc& x) { return fqc_mul_call(x, x); }
 
@@ -111,6 +112,13 @@ static __device__ __noinline__ Fq2c fq2c_sqr_call(Fq2c x) {
     Fq2c r;
     r.a = fp_mul(fp_add(x.a, x.b), fp_sub(x.a, x.b));
     r.b = fp_add(ab, ab);
+    return r;
+}
+__device__ __forceinline__ Fq2c finv(const Fq2c& x) {
+    Fq n = fp_inv(fp_add(fp_sqr(x.a), fp_sqr(x.b)));
+    Fq2c r;
+    r.a = fp_mul(x.a, n);
+    r.b = fp_neg(fp_mul(x.b, n));
     return r;
 }
 __device__ __forceinline__ Fq2c fmul(const Fq2c& x, const Fq2c& y) { return fq2c_mul_call(x, y); }

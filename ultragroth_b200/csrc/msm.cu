@@ -121,6 +121,28 @@ static typename RsSig<G>::Fn pick_rs(int v) {
     }
     throw std::runtime_error("ultragroth_b200: unknown running-sum variant");
 }
+template <class F> struct BaSig { using Fn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, XYZZ<F>*, uint32_t*, XYZZ<F>*, uint32_t, uint4*, uint4*, uint32_t*, uint32_t*); };
+template <class G>
+static typename BaSig<G>::Fn pick_ba(int v) {
+    switch (v) {
+        case 2: return k_accumulate_affine<G, 2>;
+        case 3: return k_accumulate_affine<G, 3>;
+        case 4: return k_accumulate_affine<G, 4>;
+        case 5: return k_accumulate_affine<G, 5>;
+    }
+    throw std::runtime_error("ultragroth_b200: unknown affine accumulate variant");
+}
+// variants 2x: batched-affine accumulation with inlined products, 3x: with called products (Fqc / Fq2c); x = CTAs per SM
+template <class F>
+static typename BaSig<F>::Fn select_affine(int variant) {
+    const int v = variant % 10;
+    if (variant >= 30) {
+        if constexpr (sizeof(F) == 64) return (typename BaSig<F>::Fn)pick_ba<Fq2c>(v);
+        else return (typename BaSig<F>::Fn)pick_ba<Fqc>(v);
+    }
+    return pick_ba<F>(v);
+}
+
 template <class F>
 static void select_accumulate(int variant, typename AccSig<F>::Fn& fn, size_t& smem) {
     const int v = variant % 10;
@@ -157,11 +179,18 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     // per SM (k_accumulate_s), or 0 = all-register k_accumulate.  UGB_ACC_G1 / UGB_ACC_G2 override the default.
     using AccFn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, P*, uint32_t*, P*);
     const int acc_variant = env_int_msm(g1 ? "UGB_ACC_G1" : "UGB_ACC_G2", g1 ? ACC_VARIANT_G1 : ACC_VARIANT_G2);
+    const bool affine = acc_variant >= 20;
     AccFn acc_fn = k_accumulate<F>;
+    typename BaSig<F>::Fn ba_fn = nullptr;
     size_t acc_smem = 0;
-    select_accumulate<F>(acc_variant, acc_fn, acc_smem);
     int occ = 1;
-    UG_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, acc_fn, 128, acc_smem));
+    if (affine) {
+        ba_fn = select_affine<F>(acc_variant);
+        UG_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, ba_fn, BA_BS, 0));
+    } else {
+        select_accumulate<F>(acc_variant, acc_fn, acc_smem);
+        UG_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, acc_fn, 128, acc_smem));
+    }
     occ = std::max(occ, 1);
     uint64_t max_entries = dg.n * (uint64_t)cfg.W;
     uint64_t want_threads = std::max<uint64_t>(128, (max_entries + 15) / 16);
@@ -175,7 +204,17 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     uint32_t* keys_b = (uint32_t*)ctx.workspace("msm.pkeys_b", (size_t)K1 * 4);
     P* pts_b = (P*)ctx.workspace("msm.ppts_b", (size_t)K1 * sizeof(P));
 
-    UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), acc_fn<<<blocks, 128, acc_smem, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a));
+    if (affine) {
+        // per-thread scratch lists, sized for the largest possible entry count (the real count is only known on the device)
+        const uint32_t Lmax = (uint32_t)((max_entries + T - 1) / T) + 1;
+        uint4* list_mem = (uint4*)ctx.workspace("msm.ba_list", (size_t)T * Lmax * sizeof(Affine<F>));
+        uint4* suf_mem = (uint4*)ctx.workspace("msm.ba_suf", (size_t)T * (Lmax / 2 + 1) * sizeof(F));
+        uint32_t* keys_mem = (uint32_t*)ctx.workspace("msm.ba_keys", (size_t)T * Lmax * 4);
+        uint32_t* pairs_mem = (uint32_t*)ctx.workspace("msm.ba_pairs", (size_t)T * (Lmax / 2 + 1) * 4);
+        UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), ba_fn<<<blocks, BA_BS, 0, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a, Lmax, list_mem, suf_mem, keys_mem, pairs_mem));
+    } else {
+        UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), acc_fn<<<blocks, 128, acc_smem, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a));
+    }
 
     uint32_t* kin = keys_a; P* pin = pts_a; uint32_t* kout = keys_b; P* pout = pts_b;
     uint32_t Kcur = K;
