@@ -161,12 +161,15 @@ def main():
         proof_json, public_json = prover.prove(wt_np)
     verified = None
     if rank == 0 and not args.no_verify:
+        # the product's own verifier (include/verifier.h, host C++) is the gate; the oracle's verifier cross-checks it
+        from ultragroth_b200 import verifier as uv
+        verified = uv.verify("ultragroth" if ultra else "groth16", proof_json, public_json, vkj)
         proof = og.proof_from_json(proof_json)
         public = [int(x) for x in json.loads(public_json)] if public_json != "null" else []
         if ultra:
-            verified = bool(og.ultragroth_verify(og.vk_from_ultragroth_json(vkj), proof, public))
+            verified = verified and bool(og.ultragroth_verify(og.vk_from_ultragroth_json(vkj), proof, public))
         else:
-            verified = bool(og.groth16_verify(og.vk_from_snarkjs_json(vkj), proof, public))
+            verified = verified and bool(og.groth16_verify(og.vk_from_snarkjs_json(vkj), proof, public))
         if not verified:
             raise SystemExit("bench: the proof does not verify -- refusing to report a number")
 

@@ -9,6 +9,7 @@ from oracle import bn254 as bn
 from oracle import groth16 as og
 from tests.util import g1_from_bytes, g2_from_bytes
 from ultragroth_b200 import prover as up
+from ultragroth_b200 import verifier as uv
 
 pytestmark = pytest.mark.gpu
 
@@ -74,6 +75,9 @@ def test_synth_groth16_large_verifies(ctx, logn):
     public = [int(x) for x in json.loads(uj)]
     assert og.groth16_verify(vk, og.proof_from_json(pj), public)
     assert not og.groth16_verify(vk, og.proof_from_json(pj), [(public[0] - 1) % bn.R])
+    # and under the product's own verifier C API (include/verifier.h)
+    assert uv.groth16_verify(pj, uj, vkj) == (uv.VERIFIER_VALID_PROOF, "")
+    assert uv.groth16_verify(pj, json.dumps([str((public[0] - 1) % bn.R)]), vkj)[0] == uv.VERIFIER_INVALID_PROOF
     p.close()
 
 
@@ -84,4 +88,5 @@ def test_synth_ultragroth_large_verifies(ctx):
     pj, uj = p.prove(wt)
     public = [int(x) for x in json.loads(uj)]
     assert og.ultragroth_verify(vk, og.proof_from_json(pj), public)
+    assert uv.ultra_groth_verify(pj, uj, vkj) == (uv.VERIFIER_VALID_PROOF, "")
     p.close()
