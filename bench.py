@@ -351,6 +351,10 @@ def rooflines(stats, args, nvars, n, hbm_peak, peak_src, imad_wide_peak, ultra, 
     k_ntt_pass: 64 B per element per pass (read + write), 3 vectors per launch.
     """
     out = None
+    try:
+        ncu_traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except Exception:
+        ncu_traffic = {}
     acc_l, acc_ms = stats.get("k_accumulate<G1>", (0, 0.0))
     if acc_l and acc_ms > 0:
         # exact number of digit entries the G1 accumulate launches consumed (counted by the library in profile mode)
@@ -359,7 +363,11 @@ def rooflines(stats, args, nvars, n, hbm_peak, peak_src, imad_wide_peak, ultra, 
         alg_imad = total_entries * 1360.0
         sec = acc_ms * 1e-3
         out = {"kernel": "k_accumulate<G1>", "bound": "hbm", "achieved": alg_bytes / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
-               "frac": alg_bytes / sec / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
+               "frac": alg_bytes / sec / 1e9 / hbm_peak,
+               "traffic": ncu_traffic.get("k_accumulate<G1>", {}).get("bytes_per_launch"),
+               "traffic_note": "ncu dram bytes of the largest launch (%s); achieved/launches average over all G1 MSMs of a proof, "
+                               "including the small round commitment" % ncu_traffic.get("k_accumulate<G1>", {}).get("launch"),
+               "peak_source": peak_src,
                "launches": acc_l, "ms_per_launch": acc_ms / acc_l,
                "true_bound": "int32 multiply pipe (IMAD.WIDE), not HBM: 1360 IMAD.WIDE per 68 B",
                "int_pipe": {"achieved_imad_wide_per_s": alg_imad / sec, "peak_imad_wide_per_s": imad_wide_peak,
@@ -371,7 +379,8 @@ def rooflines(stats, args, nvars, n, hbm_peak, peak_src, imad_wide_peak, ultra, 
         alg = cnt * 3 * n * 64.0  # every launch reads and writes 3 vectors of n 32-byte elements
         sec = ms * 1e-3
         ntt = {"kernel": "k_ntt_pass", "bound": "hbm", "achieved": alg / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
-               "frac": alg / sec / 1e9 / hbm_peak, "traffic": None, "launches": cnt, "ms_per_launch": ms / cnt,
+               "frac": alg / sec / 1e9 / hbm_peak,
+               "traffic": ncu_traffic.get("k_ntt_pass", {}).get("bytes_per_launch"), "launches": cnt, "ms_per_launch": ms / cnt,
                "note": "per pass: 64 B/element moved but log2(n)/(2*passes) Montgomery products of 136 IMAD.WIDE per element"}
     return out, ntt
 

@@ -126,3 +126,36 @@ def test_msm_linearity_large(ctx):
     sc = [rng.randrange(bn.R) for _ in range(n)]
     expect_k = sum((a0 + i * d) * s for i, s in enumerate(sc)) % bn.R
     assert _msm(ctx, 1, pts, sc) == bn.G1.mul_affine(bn.G1_GEN, expect_k)
+
+
+@pytest.mark.parametrize("group,logn", [(1, 22), (2, 20)])
+def test_msm_full_size_known_discrete_logs(ctx, group, logn):
+    """BASELINE-size parity (2^22 G1 / 2^20 G2 points, uniform full-width scalars): the bases are k_i*G for known k_i (made by
+    the GPU fixed-base generator, itself checked against the oracle in test_gpu_synth), so the exact answer is
+    (sum k_i*s_i mod r)*G -- one big-int dot product and one oracle scalar multiplication."""
+    import ctypes
+    import numpy as np
+    from ultragroth_b200._lib import check, lib
+    n = 1 << logn
+    rng = np.random.default_rng(1000 + logn)
+    kb = rng.integers(0, 256, size=(n, 32), dtype=np.uint8)
+    kb[:, 31] &= 0x1F
+    sb = rng.integers(0, 256, size=(n, 32), dtype=np.uint8)
+    sb[:, 31] &= 0x1F
+    bases_h = np.empty((n, 64 if group == 1 else 128), dtype=np.uint8)
+    check(lib().ugb_fixed_base_mul(ctx.handle, group, kb.ctypes.data, n, bases_h.ctypes.data))
+    bases = ctx.upload(bases_h)
+    sc = ctx.upload(sb)
+    raw = ctx.msm(group, bases, sc, n)
+    got = g1_from_bytes(raw) if group == 1 else g2_from_bytes(raw)
+    # dot product over the integers, 64-bit limbs via numpy object arithmetic would be slow: go through Python ints in chunks
+    kl = kb.view("<u8").reshape(n, 4)
+    sl = sb.view("<u8").reshape(n, 4)
+    to_int = lambda a: [int(r[0]) | int(r[1]) << 64 | int(r[2]) << 128 | int(r[3]) << 192 for r in a]
+    dot = 0
+    for lo in range(0, n, 1 << 16):
+        dot += sum(x * y for x, y in zip(to_int(kl[lo:lo + (1 << 16)]), to_int(sl[lo:lo + (1 << 16)])))
+    C, gen = (bn.G1, bn.G1_GEN) if group == 1 else (bn.G2, bn.G2_GEN)
+    assert got == C.mul_affine(gen, dot % bn.R)
+    bases.free()
+    sc.free()

@@ -90,3 +90,21 @@ def test_synth_ultragroth_large_verifies(ctx):
     assert og.ultragroth_verify(vk, og.proof_from_json(pj), public)
     assert uv.ultra_groth_verify(pj, uj, vkj) == (uv.VERIFIER_VALID_PROOF, "")
     p.close()
+
+
+def test_config1_groth16_2pow20_full_size(ctx):
+    """BASELINE.json configs[1]: synthetic Groth16 circuit, 2^20 constraints, one B200.  At this size the oracle prover is
+    out of reach, so parity is through the verifier equation (product C++ verifier and oracle verifier), a tampered input
+    must fail, and the resident prover must give a fresh valid proof on every call."""
+    zk, wt, vkj = ctx.synth(20, seed=0xB200 + 20)
+    p = up.Prover(zk)
+    del zk
+    pj, uj = p.prove(wt)
+    public = [int(x) for x in json.loads(uj)]
+    assert uv.groth16_verify(pj, uj, vkj) == (uv.VERIFIER_VALID_PROOF, "")
+    assert og.groth16_verify(og.vk_from_snarkjs_json(vkj), og.proof_from_json(pj), public)
+    assert uv.groth16_verify(pj, json.dumps([str((public[0] + 1) % bn.R)]), vkj)[0] == uv.VERIFIER_INVALID_PROOF
+    pj2, uj2 = p.prove(wt)
+    assert pj2 != pj and uj2 == uj
+    assert uv.groth16_verify(pj2, uj2, vkj) == (uv.VERIFIER_VALID_PROOF, "")
+    p.close()
