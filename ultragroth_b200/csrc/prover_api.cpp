@@ -264,14 +264,17 @@ public:
 
     struct Lookup { std::vector<uint32_t> chunks, freqs, widx, pidx; };
 
-    const uint8_t* check_witness(const BinFile& wtns, Lookup& lk) {
+    const uint8_t* check_witness(const BinFile& wtns) {
         WtnsHeader wh = load_wtns_header(wtns);
         if (hdr.nVars != wh.nVars)
             throw InvalidWitnessLengthException("Invalid witness length. Circuit: " + std::to_string(hdr.nVars) +
                                                 ", witness: " + std::to_string(wh.nVars));
         if (!prime_is_bn254_r(wh.prime, wh.n8)) throw std::invalid_argument("different wtns curve");
         if (wtns.size(2) < (uint64_t)hdr.nVars * 32) throw std::range_error("wtns section too short: signals");
-        // LookupInfo (src/prover.cpp:287-292, src/ultra_groth.hpp:22-61): four u32 arrays
+        return wtns.data(2);
+    }
+    // LookupInfo (src/prover.cpp:287-292, src/ultra_groth.hpp:22-61): four u32 arrays
+    void load_lookup(const BinFile& wtns, Lookup& lk) {
         auto u32s = [&](uint32_t id, std::vector<uint32_t>& v) {
             uint64_t cnt = wtns.size(id) >> 2;
             v.resize(cnt);
@@ -282,7 +285,11 @@ public:
             // the reference iterates wtns_indxs_len entries of both arrays
             if (lk.pidx.size() < lk.widx.size()) throw std::range_error("wtns push index section shorter than witness index section");
         }
-        return wtns.data(2);
+    }
+    const uint8_t* check_witness(const BinFile& wtns, Lookup& lk) {
+        const uint8_t* w = check_witness(wtns);
+        load_lookup(wtns, lk);
+        return w;
     }
     // round 1, device half: upload + MSM(round_pointsC, round_wtns) over this prover's point range
     void round_msm(const uint8_t* w, HG1XYZZ& partial) {
@@ -291,13 +298,15 @@ public:
     }
     // commitment = (sum of the round MSM) + r_k * final_delta1 (src/ultra_groth.cpp:161-184), then the challenge,
     // the lookup fill and the final-round MSMs over this prover's point range
-    void final_msms(HG1XYZZ commit, const Scalar& rk, const Lookup& lk, HG1Affine& commit_aff, ProofMsms& m) {
+    void final_msms(HG1XYZZ commit, const Scalar& rk, const Lookup& lk, HG1Affine& commit_aff, ProofMsms& m, bool staged = false) {
         HG1XYZZ fdelta1 = from_affine_bytes<HFq>(hdr.final_delta1);
         pt_add(commit, pt_mul(fdelta1, rk));
         commit_aff = pt_to_affine(commit);
         HFr rand_mont = derive_challenge(commit_aff);  // src/ultra_groth.cpp:32-58
-        dev->ultra_lookup(lk.chunks.data(), (uint32_t)lk.chunks.size(), lk.freqs.data(), (uint32_t)lk.freqs.size(), lk.widx.data(),
-                          lk.pidx.data(), (uint32_t)lk.widx.size(), rand_mont);
+        if (!staged)
+            dev->ultra_lookup_stage(lk.chunks.data(), (uint32_t)lk.chunks.size(), lk.freqs.data(), (uint32_t)lk.freqs.size(), lk.widx.data(),
+                                    lk.pidx.data(), (uint32_t)lk.widx.size());
+        dev->ultra_lookup_apply(rand_mont);
         dev->ultra_final_msms(m);
     }
     void finish(const ProofMsms& m, const Scalar& rk, const HG1Affine& commit_aff, std::string& stringProof, std::string& stringPublic) {
@@ -314,14 +323,19 @@ public:
     }
     void prove(const void* wtns_buffer, unsigned long long wtns_size, std::string& stringProof, std::string& stringPublic) {
         BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
+        const uint8_t* w = check_witness(wtns);
+        // the witness copy is asynchronous: the lookup arrays are unpacked, range-checked and staged while it is in flight
+        dev->ultra_upload_witness(w);
         Lookup lk;
-        const uint8_t* w = check_witness(wtns, lk);
+        load_lookup(wtns, lk);
+        dev->ultra_lookup_stage(lk.chunks.data(), (uint32_t)lk.chunks.size(), lk.freqs.data(), (uint32_t)lk.freqs.size(), lk.widx.data(),
+                                lk.pidx.data(), (uint32_t)lk.widx.size());
         HG1XYZZ commit;
-        round_msm(w, commit);
+        dev->ultra_round_msm(commit);
         Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
         HG1Affine commit_aff;
         ProofMsms m;
-        final_msms(commit, rk, lk, commit_aff, m);
+        final_msms(commit, rk, lk, commit_aff, m, true);
         finish(m, rk, commit_aff, stringProof, stringPublic);
     }
     unsigned long long proofBufferMinSize() const { return ProofBufferMinSizeUltraGroth(); }

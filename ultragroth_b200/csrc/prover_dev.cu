@@ -448,8 +448,8 @@ void ProverDevice::ultra_round_msm(HG1XYZZ& out) {
     msm_g1_finish(ctx, d, "round", &out);
 }
 
-void ProverDevice::ultra_lookup(const uint32_t* chunks, uint32_t chunks_len, const uint32_t* freqs, uint32_t freqs_len,
-                                const uint32_t* wtns_idx, const uint32_t* push_idx, uint32_t idx_len, const HFr& rand_mont) {
+void ProverDevice::ultra_lookup_stage(const uint32_t* chunks, uint32_t chunks_len, const uint32_t* freqs, uint32_t freqs_len,
+                                      const uint32_t* wtns_idx, const uint32_t* push_idx, uint32_t idx_len) {
     DeviceCtx& ctx = *ctx_;
     ctx.activate();
     // bounds (the reference trusts the file; out-of-range indices would be wild writes there)
@@ -463,14 +463,25 @@ void ProverDevice::ultra_lookup(const uint32_t* chunks, uint32_t chunks_len, con
     uint32_t* d_freqs = (uint32_t*)ctx.workspace("lk.freqs", (size_t)freqs_len * 4 + 16);
     uint32_t* d_widx = (uint32_t*)ctx.workspace("lk.widx", (size_t)idx_len * 4 + 16);
     uint32_t* d_pidx = (uint32_t*)ctx.workspace("lk.pidx", (size_t)idx_len * 4 + 16);
-    Fr* d_inv2 = (Fr*)ctx.workspace("lk.inv2", (size_t)freqs_len * 32 + 32);
-    Fr* d_prod = (Fr*)ctx.workspace("lk.prod", (size_t)freqs_len * 32 + 32);
     if (chunks_len) UG_CUDA_CHECK(cudaMemcpyAsync(d_chunks, chunks, (size_t)chunks_len * 4, cudaMemcpyHostToDevice, ctx.stream));
     if (freqs_len) UG_CUDA_CHECK(cudaMemcpyAsync(d_freqs, freqs, (size_t)freqs_len * 4, cudaMemcpyHostToDevice, ctx.stream));
     if (idx_len) {
         UG_CUDA_CHECK(cudaMemcpyAsync(d_widx, wtns_idx, (size_t)idx_len * 4, cudaMemcpyHostToDevice, ctx.stream));
         UG_CUDA_CHECK(cudaMemcpyAsync(d_pidx, push_idx, (size_t)idx_len * 4, cudaMemcpyHostToDevice, ctx.stream));
     }
+    lk_chunks_len_ = chunks_len; lk_freqs_len_ = freqs_len; lk_idx_len_ = idx_len;
+}
+
+void ProverDevice::ultra_lookup_apply(const HFr& rand_mont) {
+    DeviceCtx& ctx = *ctx_;
+    ctx.activate();
+    const uint32_t chunks_len = lk_chunks_len_, freqs_len = lk_freqs_len_, idx_len = lk_idx_len_;
+    uint32_t* d_chunks = (uint32_t*)ctx.workspace("lk.chunks", (size_t)chunks_len * 4 + 16);
+    uint32_t* d_freqs = (uint32_t*)ctx.workspace("lk.freqs", (size_t)freqs_len * 4 + 16);
+    uint32_t* d_widx = (uint32_t*)ctx.workspace("lk.widx", (size_t)idx_len * 4 + 16);
+    uint32_t* d_pidx = (uint32_t*)ctx.workspace("lk.pidx", (size_t)idx_len * 4 + 16);
+    Fr* d_inv2 = (Fr*)ctx.workspace("lk.inv2", (size_t)freqs_len * 32 + 32);
+    Fr* d_prod = (Fr*)ctx.workspace("lk.prod", (size_t)freqs_len * 32 + 32);
     Fr rm, rr;
     memcpy(&rm, &rand_mont, 32);
     HFr raw = from_mont(rand_mont);
@@ -483,7 +494,7 @@ void ProverDevice::ultra_lookup(const uint32_t* chunks, uint32_t chunks_len, con
         int blocks = (int)std::min<uint64_t>(((uint64_t)idx_len + 255) / 256, (uint64_t)ctx.sm_count * 8);
         UG_KERNEL(ctx, "k_lookup_push", k_lookup_push<<<blocks, 256, 0, ctx.stream>>>(d_widx, d_pidx, idx_len, d_chunks, chunks_len, freqs_len, rr, d_inv2, d_prod, (Fr*)w_));
     }
-    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));  // host index arrays are borrowed
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));  // the staged host index arrays are borrowed until here
 }
 
 void ProverDevice::ultra_final_msms(ProofMsms& out) {

@@ -52,8 +52,11 @@ public:
     // ---- UltraGroth (src/ultra_groth.cpp:401-462) ----
     void ultra_upload_witness(const uint8_t* witness);
     void ultra_round_msm(HG1XYZZ& out);                                   // execute_round's MSM (:168)
-    void ultra_lookup(const uint32_t* chunks, uint32_t chunks_len, const uint32_t* freqs, uint32_t freqs_len, const uint32_t* wtns_idx,
-                      const uint32_t* push_idx, uint32_t idx_len, const HFr& rand_mont);  // compute_lookup (:62-106)
+    // compute_lookup (:62-106) in two halves: _stage range-checks the four index arrays and copies them to HBM (asynchronous; the
+    // host arrays must stay valid until the next stream synchronisation), _apply runs the kernels once the challenge is known
+    void ultra_lookup_stage(const uint32_t* chunks, uint32_t chunks_len, const uint32_t* freqs, uint32_t freqs_len, const uint32_t* wtns_idx,
+                            const uint32_t* push_idx, uint32_t idx_len);
+    void ultra_lookup_apply(const HFr& rand_mont);
     void ultra_final_msms(ProofMsms& out);                                // execute_final_round's MSMs + H
     void download_witness(uint8_t* dst, uint64_t first, uint64_t count);  // signals after the lookup fill
 
@@ -90,6 +93,8 @@ private:
     void* long_segs_ = nullptr;     // the long rows cut into <= SPMV_SEG-term segments, one CTA each
     void* long_partial_ = nullptr;  // one Fr partial sum per segment
     uint32_t n_long_segs_ = 0;
+    // staged lookup arrays (ultra_lookup_stage)
+    uint32_t lk_chunks_len_ = 0, lk_freqs_len_ = 0, lk_idx_len_ = 0;
     // per-proof buffers
     void *w_ = nullptr, *a_ = nullptr, *b_ = nullptr, *c_ = nullptr;
     std::vector<cudaEvent_t> ev_;
