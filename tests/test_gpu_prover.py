@@ -77,3 +77,19 @@ def test_groth16_oneshot_and_errors(fixture):
         p.prove(b"wtnX" + wt[4:])
     assert e.value.code == up.PROVER_ERROR
     p.close()
+
+
+def test_groth16_matches_committed_golden_proof(fixture):
+    """The CUDA prover against the committed golden proof (tests/golden/testdata_proof.json): no oracle run involved."""
+    import hashlib
+    zk, wt, vk = fixture
+    g = json.load(open(os.path.join(os.path.dirname(GOLD), "testdata_proof.json")))
+    p = up.Prover(zk, "groth16")
+    p.set_blinding(int(g["r"], 16), int(g["s"], 16))
+    pj, uj = p.prove(wt)
+    assert json.loads(pj) == g["proof"] and json.loads(uj) == g["public"]
+    assert hashlib.sha256(p.last_h(g["h_count"])).hexdigest() == g["h_sha256"]
+    p.close()
+    # the one-shot entry point (no window tables) gives the same verdict
+    pj1, uj1 = up.prove_oneshot(zk, wt, "groth16")
+    assert og.groth16_verify(vk, og.proof_from_json(pj1), [int(x) for x in json.loads(uj1)])

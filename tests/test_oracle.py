@@ -218,3 +218,24 @@ def test_ntt_root_convention():
     w = bn.fr_root(28)
     assert pow(w, 1 << 28, bn.R) == 1 and pow(w, 1 << 27, bn.R) == bn.R - 1
     assert bn.fr_root(3) == pow(w, 1 << 25, bn.R)
+
+
+def test_oracle_reproduces_golden_testdata_proof():
+    """tests/golden/testdata_proof.json freezes the proof of the reference fixture for fixed r, s (generator:
+    tests/golden/make_proof_vectors.py): the oracle must keep producing exactly these bytes, and the product's verifier
+    must accept them against the reference's verification_key.json."""
+    import hashlib
+    import json
+    import os
+    from oracle import groth16 as og
+    from ultragroth_b200 import verifier as uv
+    gold = os.path.join(os.path.dirname(__file__), "golden")
+    g = json.load(open(os.path.join(gold, "testdata_proof.json")))
+    zk = open(os.path.join(gold, "ref_testdata", "circuit_final.zkey"), "rb").read()
+    wt = open(os.path.join(gold, "ref_testdata", "witness.wtns"), "rb").read()
+    proof, public, inter = og.groth16_prove(zk, wt, int(g["r"], 16), int(g["s"], 16), want_intermediates=True)
+    assert json.loads(og.proof_to_json(proof)) == g["proof"]
+    assert json.loads(og.public_to_json(public)) == g["public"]
+    assert hashlib.sha256(b"".join(int(x).to_bytes(32, "little") for x in inter["h"])).hexdigest() == g["h_sha256"]
+    vkj = open(os.path.join(gold, "ref_testdata", "verification_key.json")).read()
+    assert uv.groth16_verify(json.dumps(g["proof"]), json.dumps(g["public"]), vkj) == (uv.VERIFIER_VALID_PROOF, "")

@@ -179,7 +179,8 @@ int pick_device() {
 
 class ProverBase {
 public:
-    ProverBase(const void* zkey_buffer, unsigned long long zkey_size, bool ultra, uint32_t shard_rank = 0, uint32_t shard_world = 1)
+    ProverBase(const void* zkey_buffer, unsigned long long zkey_size, bool ultra, uint32_t shard_rank = 0, uint32_t shard_world = 1,
+               bool tables = true)
         : zkey(zkey_buffer, zkey_size, "zkey", 1), hdr(load_zkey_header(zkey, ultra)) {
         if (!prime_is_bn254_r(hdr.rPrime, hdr.n8r)) throw std::invalid_argument("zkey curve not supported");
         // the header points (alpha, beta, delta...) are copied: the zkey buffer is only borrowed during create
@@ -187,7 +188,7 @@ public:
         hdr_copy.assign(zkey.data(2), zkey.data(2) + zkey.size(2));
         BinFile::Section s{hdr_copy.data(), hdr_copy.size()};
         rebase(s);
-        dev.reset(new ProverDevice(pick_device(), zkey, hdr, shard_rank, shard_world));
+        dev.reset(new ProverDevice(pick_device(), zkey, hdr, shard_rank, shard_world, tables));
     }
     virtual ~ProverBase() {}
 
@@ -220,8 +221,8 @@ static ProofMsms sum_partials(const ProofMsms* parts, uint32_t count) {
 
 class Groth16Prover : public ProverBase {
 public:
-    Groth16Prover(const void* zkey_buffer, unsigned long long zkey_size, uint32_t shard_rank = 0, uint32_t shard_world = 1)
-        : ProverBase(zkey_buffer, zkey_size, false, shard_rank, shard_world) {}
+    Groth16Prover(const void* zkey_buffer, unsigned long long zkey_size, uint32_t shard_rank = 0, uint32_t shard_world = 1, bool tables = true)
+        : ProverBase(zkey_buffer, zkey_size, false, shard_rank, shard_world, tables) {}
 
     const uint8_t* check_witness(const void* wtns_buffer, unsigned long long wtns_size) {
         BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
@@ -259,8 +260,8 @@ public:
 
 class UltraGrothProver : public ProverBase {
 public:
-    UltraGrothProver(const void* zkey_buffer, unsigned long long zkey_size, uint32_t shard_rank = 0, uint32_t shard_world = 1)
-        : ProverBase(zkey_buffer, zkey_size, true, shard_rank, shard_world) {}
+    UltraGrothProver(const void* zkey_buffer, unsigned long long zkey_size, uint32_t shard_rank = 0, uint32_t shard_world = 1, bool tables = true)
+        : ProverBase(zkey_buffer, zkey_size, true, shard_rank, shard_world, tables) {}
 
     struct Lookup { std::vector<uint32_t> chunks, freqs, widx, pidx; };
 
@@ -405,11 +406,11 @@ int prover_prove_impl(void* prover_object, const void* wtns_buffer, unsigned lon
 
 template <class P>
 int prover_create_impl(void** prover_object, const void* zkey_buffer, unsigned long long zkey_size, char* error_msg,
-                       unsigned long long error_msg_maxsize) {
+                       unsigned long long error_msg_maxsize, bool tables = true) {
     API_TRY
     if (prover_object == NULL) throw std::invalid_argument("Null prover object");
     if (zkey_buffer == NULL) throw std::invalid_argument("Null zkey buffer");
-    *prover_object = static_cast<ProverBase*>(new P(zkey_buffer, zkey_size));
+    *prover_object = static_cast<ProverBase*>(new P(zkey_buffer, zkey_size, 0, 1, tables));
     API_CATCH_CREATE
 }
 
@@ -502,7 +503,8 @@ int groth16_prover(const void* zkey_buffer, unsigned long long zkey_size, const 
                    char* proof_buffer, unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
                    unsigned long long error_msg_maxsize) {
     void* prover = NULL;
-    int error = groth16_prover_create(&prover, zkey_buffer, zkey_size, error_msg, error_msg_maxsize);
+    // one proof only: the window tables (1.3 s to build at 2^22) cannot pay for themselves, so the one-level bases are used
+    int error = prover_create_impl<Groth16Prover>(&prover, zkey_buffer, zkey_size, error_msg, error_msg_maxsize, false);
     if (error != PROVER_OK) return error;
     error = groth16_prover_prove(prover, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
                                  error_msg_maxsize);
@@ -513,7 +515,7 @@ int ultra_groth_prover(const void* zkey_buffer, unsigned long long zkey_size, co
                        char* proof_buffer, unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size,
                        char* error_msg, unsigned long long error_msg_maxsize) {
     void* prover = NULL;
-    int error = ultra_groth_prover_create(&prover, zkey_buffer, zkey_size, error_msg, error_msg_maxsize);
+    int error = prover_create_impl<UltraGrothProver>(&prover, zkey_buffer, zkey_size, error_msg, error_msg_maxsize, false);
     if (error != PROVER_OK) return error;
     error = ultra_groth_prover_prove(prover, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
                                      error_msg_maxsize);
@@ -523,24 +525,26 @@ int ultra_groth_prover(const void* zkey_buffer, unsigned long long zkey_size, co
 int groth16_prover_zkey_file(const char* zkey_file_path, const void* wtns_buffer, unsigned long long wtns_size, char* proof_buffer,
                              unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
                              unsigned long long error_msg_maxsize) {
-    void* prover = NULL;
-    int error = groth16_prover_create_zkey_file(&prover, zkey_file_path, error_msg, error_msg_maxsize);
-    if (error != PROVER_OK) return error;
-    error = groth16_prover_prove(prover, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
-                                 error_msg_maxsize);
-    groth16_prover_destroy(prover);
-    return error;
+    std::vector<uint8_t> zkey;
+    API_TRY
+    zkey = read_file(zkey_file_path);
+    }
+    catch (std::exception & e) { CopyError(error_msg, error_msg_maxsize, e.what()); return PROVER_ERROR; }
+    catch (...) { CopyError(error_msg, error_msg_maxsize, "unknown error"); return PROVER_ERROR; }
+    return groth16_prover(zkey.data(), zkey.size(), wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
+                     error_msg_maxsize);
 }
 int ultra_groth_prover_zkey_file(const char* zkey_file_path, const void* wtns_buffer, unsigned long long wtns_size, char* proof_buffer,
                                  unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
                                  unsigned long long error_msg_maxsize) {
-    void* prover = NULL;
-    int error = ultra_groth_prover_create_zkey_file(&prover, zkey_file_path, error_msg, error_msg_maxsize);
-    if (error != PROVER_OK) return error;
-    error = ultra_groth_prover_prove(prover, wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
-                                     error_msg_maxsize);
-    ultra_groth_prover_destroy(prover);
-    return error;
+    std::vector<uint8_t> zkey;
+    API_TRY
+    zkey = read_file(zkey_file_path);
+    }
+    catch (std::exception & e) { CopyError(error_msg, error_msg_maxsize, e.what()); return PROVER_ERROR; }
+    catch (...) { CopyError(error_msg, error_msg_maxsize, "unknown error"); return PROVER_ERROR; }
+    return ultra_groth_prover(zkey.data(), zkey.size(), wtns_buffer, wtns_size, proof_buffer, proof_size, public_buffer, public_size, error_msg,
+                     error_msg_maxsize);
 }
 
 // ---- extensions declared in include/ultragroth_b200.h ---------------------------------------------

@@ -165,7 +165,7 @@ static int ilog2_exact(uint32_t n) {
     return k;
 }
 
-ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h, uint32_t shard_rank, uint32_t shard_world)
+ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h, uint32_t shard_rank, uint32_t shard_world, bool tables)
     : nVars(h.nVars), nPublic(h.nPublic), domainSize(h.domainSize), ultra_(h.ultra) {
     if (shard_world == 0 || shard_rank >= shard_world) throw std::invalid_argument("bad shard rank / world");
     shard_range(nVars, shard_world, shard_rank, w_lo_, w_hi_);
@@ -303,7 +303,7 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h,
     // window tables: 2^(c*w) multiples of every base, resident next to the bases they replace (UGB_MSM_PRE=0: off)
     {
         const char* e = getenv("UGB_MSM_PRE");
-        pre_ = !(e && atoi(e) == 0);
+        pre_ = tables && !(e && atoi(e) == 0);
         if (pre_) {
             auto tabulate = [&](void*& base, int group, uint64_t count, MsmConfig& cfg) {
                 MsmTable t = msm_build_table(ctx, group, base, count);

@@ -31,7 +31,8 @@ public:
     // shard_rank / shard_world: point-range sharding: this device keeps only slice
     // shard_range(count, world, rank) of every base array resident and its MSMs return PARTIAL sums; the
     // witness, the coefficients and the H pipeline are replicated on every shard.
-    ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& hdr, uint32_t shard_rank = 0, uint32_t shard_world = 1);
+    // tables = false: skip the window-table build (one-shot *_prover calls: the 2^(c*k) multiples only pay off across proofs)
+    ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& hdr, uint32_t shard_rank = 0, uint32_t shard_world = 1, bool tables = true);
     static void shard_range(uint64_t n, uint32_t world, uint32_t rank, uint64_t& lo, uint64_t& hi) {
         const uint64_t base = n / world, rem = n % world;
         lo = rank * base + std::min<uint64_t>(rank, rem);
