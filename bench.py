@@ -256,6 +256,14 @@ def main():
             "wall_ms_per_step": 1000.0 * t_wall / args.steps,
             "setup_s": round(t_setup, 2), "create_s": round(t_create, 2),
         }
+        # second half of BASELINE.json's metric: G1 MSM points/s, taken from the proof's own H MSM (domainSize dense full-width
+        # scalars against the resident table, sort + accumulate + reduce) and the A MSM (nVars witness scalars); whole job = x world
+        if stage.get("msm_h", 0) > 0 and stage.get("msm_a", 0) > 0:
+            line["g1_msm"] = {
+                "h_points_per_s": world * n / ((stage["msm_h"] + stage["sort_h"]) * 1e-3), "h_points": n, "h_ms": stage["msm_h"] + stage["sort_h"],
+                "a_points_per_s": world * nvars / (stage["msm_a"] * 1e-3), "a_points": nvars, "a_ms": stage["msm_a"],
+                "note": "per-proof MSMs over resident window tables (c=22); standalone ad-hoc-base sweep: profiles/r01_sweep_g1.jsonl"}
+        line["prove_latency_ms"] = {"resident": 1000.0 * t_dev / args.steps, "e2e": 1000.0 * t_e2e / args.steps}
         line["roofline"], line["roofline_ntt"] = rooflines(stats, args, nvars, n, hbm_peak, peak_src, imad_wide, ultra, chunks, lookup_bits)
         if not args.no_cpu and world == 1:
             try:

@@ -71,18 +71,6 @@ UG_HD Fq2 finv(const Fq2& x) {
 }
 
 #if defined(__CUDACC__)
-// Fqc: Fq with a CALLED Montgomery product (same trick as Fq2c below, for the G1 bucket-reduction kernels).
-struct FqcParams : FqParams {};
-using Fqc = Fp<FqcParams>;
-static __device__ __noinline__ Fqc fqc_mul_call(Fqc x, Fqc y) { return fp_mul(x, y); }
-__device__ __forceinline__ Fqc fadd(const Fqc& x, const Fqc& y) { return fp_add(x, y); }
-__device__ __forceinline__ Fqc fsub(const Fqc& x, const Fqc& y) { return fp_sub(x, y); }
-__device__ __forceinline__ Fqc fneg(const Fqc& x) { return fp_neg(x); }
-__device__ __forceinline__ Fqc fdbl(const Fqc& x) { return fp_add(x, x); }
-__device__ __forceinline__ Fqc finv(const Fqc& x) { return fp_inv(x); }
-__device__ __forceinline__ Fqc fmul(const Fqc& x, const Fqc& y) { return fqc_mul_call(x, y); }
-__device__ __forceinline__ Fqc fsqr(const Fqc& x) { return fqc_mul_call(x, x); }
-
 // Fq2c: the same field and layout as Fq2, but its two products are REAL calls (arguments and result by value, which the
 // device ABI keeps in registers: no stack traffic).  A kernel instantiated on Fq2c is ~10x smaller than on Fq2:
 // k_running_sum<Fq2> is 500 KB of SASS, several times the SM's instruction cache.

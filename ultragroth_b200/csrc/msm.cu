@@ -7,7 +7,7 @@
 
 namespace ug {
 
-// default kernel variants (0 = all-register kernels; n = shared-memory accumulators at n CTAs per SM), see msm.cuh
+// default kernel variants, see "kernel variants" below
 constexpr int ACC_VARIANT_G1 = 0, ACC_VARIANT_G2 = 12, RS_VARIANT_G1 = 0, RS_VARIANT_G2 = 12;
 
 static int env_int_msm(const char* name, int dflt) {
@@ -93,77 +93,43 @@ void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d
 }
 
 // ---- kernel variants ------------------------------------------------------------------------------
-// variant = 0: all-register kernel; n in 2..6: shared-memory accumulators at n CTAs per SM; +10: instantiate on
-// Fqc / Fq2c (called field products, small code) instead of Fq / Fq2 -- same memory layout, so the pointers are only re-typed.
+// Selected by UGB_ACC_G1 / UGB_ACC_G2 / UGB_RS_G1 / UGB_RS_G2 (defaults above); only the variants that earned a place after
+// the round-1 sweeps (tools/variants.sh) are compiled:
+//    0   all-register kernel (k_accumulate / k_running_sum)                                           G1 default, G2
+//   12   G2 only: accumulator(s) in shared memory, 2 CTAs/SM                                          G2 default
+//   24   G1 only: batched-affine accumulation (k_accumulate_affine, 4 CTAs/SM)                        opt-in, slower
+//   33   G2 only: batched-affine accumulation, 3 CTAs/SM                                              opt-in, slower
+// G2 kernels are all instantiated on Fq2c (msm_g2_launch): Fq2's memory layout with CALLED products.
 template <class F> struct AccSig { using Fn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, XYZZ<F>*, uint32_t*, XYZZ<F>*); };
 template <class F> struct RsSig { using Fn = void (*)(const XYZZ<F>*, uint32_t, uint32_t, uint32_t, uint32_t, XYZZ<F>*, XYZZ<F>*); };
-
-template <class G>
-static typename AccSig<G>::Fn pick_acc(int v) {
-    switch (v) {
-        case 0: return k_accumulate<G>;
-        case 2: return k_accumulate_s<G, 2>;
-        case 3: return k_accumulate_s<G, 3>;
-        case 4: return k_accumulate_s<G, 4>;
-        case 5: return k_accumulate_s<G, 5>;
-        case 6: return k_accumulate_s<G, 6>;
-    }
-    throw std::runtime_error("ultragroth_b200: unknown accumulate variant");
-}
-template <class G>
-static typename RsSig<G>::Fn pick_rs(int v) {
-    switch (v) {
-        case 0: return k_running_sum<G>;
-        case 2: return k_running_sum_s<G, 2>;
-        case 3: return k_running_sum_s<G, 3>;
-        case 4: return k_running_sum_s<G, 4>;
-        case 5: return k_running_sum_s<G, 5>;
-    }
-    throw std::runtime_error("ultragroth_b200: unknown running-sum variant");
-}
 template <class F> struct BaSig { using Fn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, XYZZ<F>*, uint32_t*, XYZZ<F>*, uint32_t, uint4*, uint4*, uint32_t*, uint32_t*); };
-template <class G>
-static typename BaSig<G>::Fn pick_ba(int v) {
-    switch (v) {
-        case 2: return k_accumulate_affine<G, 2>;
-        case 3: return k_accumulate_affine<G, 3>;
-        case 4: return k_accumulate_affine<G, 4>;
-        case 5: return k_accumulate_affine<G, 5>;
+
+template <class F>
+static typename BaSig<F>::Fn select_affine(int variant) {
+    if constexpr (sizeof(F) == 64) {
+        if (variant == 33) return k_accumulate_affine<F, 3>;
+    } else {
+        if (variant == 24) return k_accumulate_affine<F, 4>;
     }
     throw std::runtime_error("ultragroth_b200: unknown affine accumulate variant");
 }
-// variants 2x: batched-affine accumulation with inlined products, 3x: with called products (Fqc / Fq2c); x = CTAs per SM
-template <class F>
-static typename BaSig<F>::Fn select_affine(int variant) {
-    const int v = variant % 10;
-    if (variant >= 30) {
-        if constexpr (sizeof(F) == 64) return (typename BaSig<F>::Fn)pick_ba<Fq2c>(v);
-        else return (typename BaSig<F>::Fn)pick_ba<Fqc>(v);
-    }
-    return pick_ba<F>(v);
-}
-
 template <class F>
 static void select_accumulate(int variant, typename AccSig<F>::Fn& fn, size_t& smem) {
-    const int v = variant % 10;
-    smem = v ? 128 * sizeof(XYZZ<F>) : 0;
+    smem = 0;
+    if (variant == 0) { fn = k_accumulate<F>; return; }
     if constexpr (sizeof(F) == 64) {
-        if (variant >= 10) { fn = (typename AccSig<F>::Fn)pick_acc<Fq2c>(v); return; }
-    } else {
-        if (variant >= 10) { fn = (typename AccSig<F>::Fn)pick_acc<Fqc>(v); return; }
+        if (variant == 12) { fn = k_accumulate_s<F, 2>; smem = 128 * sizeof(XYZZ<F>); return; }
     }
-    fn = pick_acc<F>(v);
+    throw std::runtime_error("ultragroth_b200: unknown accumulate variant");
 }
 template <class F>
 static void select_running_sum(int variant, typename RsSig<F>::Fn& fn, size_t& smem) {
-    const int v = variant % 10;
-    smem = v ? 2 * 128 * sizeof(XYZZ<F>) : 0;
+    smem = 0;
+    if (variant == 0) { fn = k_running_sum<F>; return; }
     if constexpr (sizeof(F) == 64) {
-        if (variant >= 10) { fn = (typename RsSig<F>::Fn)pick_rs<Fq2c>(v); return; }
-    } else {
-        if (variant >= 10) { fn = (typename RsSig<F>::Fn)pick_rs<Fqc>(v); return; }
+        if (variant == 12) { fn = k_running_sum_s<F, 2>; smem = 2 * 128 * sizeof(XYZZ<F>); return; }
     }
-    fn = pick_rs<F>(v);
+    throw std::runtime_error("ultragroth_b200: unknown running-sum variant");
 }
 
 template <class F>
@@ -278,7 +244,8 @@ void msm_g1_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, con
     msm_launch_impl<Fq>(ctx, (const G1Affine*)d_bases, dg, slot);
 }
 void msm_g2_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot) {
-    msm_launch_impl<Fq2>(ctx, (const G2Affine*)d_bases, dg, slot);
+    // every G2 kernel is instantiated on Fq2c (Fq2's layout, CALLED products): an inlined Fq2 kernel is 200-500 KB of SASS
+    msm_launch_impl<Fq2c>(ctx, (const Affine<Fq2c>*)d_bases, dg, slot);
 }
 
 // ---- resident window tables ----------------------------------------------------------------------
@@ -307,7 +274,7 @@ MsmTable msm_build_table(DeviceCtx& ctx, int group, const void* d_bases, uint64_
     t.cfg = msm_pick_config(n, force_c, true);
     if ((uint64_t)n * t.cfg.W >= (1ull << 31)) throw std::runtime_error("ultragroth_b200: MSM table too large for 31-bit indices");
     t.d_table = group == 1 ? build_table_impl<Fq>(ctx, (const G1Affine*)d_bases, n, t.cfg)
-                           : build_table_impl<Fq2>(ctx, (const G2Affine*)d_bases, n, t.cfg);
+                           : build_table_impl<Fq2c>(ctx, (const Affine<Fq2c>*)d_bases, n, t.cfg);
     return t;
 }
 }  // namespace ug
