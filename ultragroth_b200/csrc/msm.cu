@@ -100,9 +100,9 @@ void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d
 //   24   G1 only: batched-affine accumulation (k_accumulate_affine, 4 CTAs/SM)                        opt-in, slower
 //   33   G2 only: batched-affine accumulation, 3 CTAs/SM                                              opt-in, slower
 // G2 kernels are all instantiated on Fq2c (msm_g2_launch): Fq2's memory layout with CALLED products.
-template <class F> struct AccSig { using Fn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, XYZZ<F>*, uint32_t*, XYZZ<F>*); };
+template <class F> struct AccSig { using Fn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, XYZZ<F>*, uint32_t*, XYZZ<F>*, uint32_t, uint32_t); };
 template <class F> struct RsSig { using Fn = void (*)(const XYZZ<F>*, uint32_t, uint32_t, uint32_t, uint32_t, XYZZ<F>*, XYZZ<F>*); };
-template <class F> struct BaSig { using Fn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, XYZZ<F>*, uint32_t*, XYZZ<F>*, uint32_t, uint4*, uint4*, uint32_t*, uint32_t*); };
+template <class F> struct BaSig { using Fn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, XYZZ<F>*, uint32_t*, XYZZ<F>*, uint32_t, uint32_t, uint32_t, uint4*, uint4*, uint32_t*, uint32_t*); };
 
 template <class F>
 static typename BaSig<F>::Fn select_affine(int variant) {
@@ -133,17 +133,22 @@ static void select_running_sum(int variant, typename RsSig<F>::Fn& fn, size_t& s
 }
 
 template <class F>
-static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmDigits& dg, const std::string& slot) {
+// nb base arrays that pair with the SAME sorted digits (A, B1, C of a proof) go through together: one accumulate launch each
+// into consecutive bucket sets, then ONE pass of the latency-bound tail (segmented merge, running sums, bit sums) over all of
+// them -- the tail's serial chains are paid once instead of nb times and its grids are nb times fuller.
+static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* const* d_bases_v, int nb, const MsmDigits& dg, const std::string* slots) {
     ctx.activate();
     const MsmConfig& cfg = dg.cfg;
     const bool g1 = sizeof(F) == 32;
     using P = XYZZ<F>;
-    P* buckets = (P*)ctx.workspace("msm.buckets", (size_t)cfg.NB * sizeof(P));
-    UG_CUDA_CHECK(cudaMemsetAsync(buckets, 0, (size_t)cfg.NB * sizeof(P), ctx.stream));
+    const uint32_t NBT = (uint32_t)nb * cfg.NB;  // buckets of the whole batch
+    if ((uint64_t)nb * cfg.NB >= (1ull << 31)) throw std::runtime_error("ultragroth_b200: MSM batch has too many buckets");
+    P* buckets = (P*)ctx.workspace("msm.buckets", (size_t)NBT * sizeof(P));
+    UG_CUDA_CHECK(cudaMemsetAsync(buckets, 0, (size_t)NBT * sizeof(P), ctx.stream));
 
     // accumulate: T threads over the sorted entries.  Kernel variant: the XYZZ accumulator in shared memory at MINB CTAs
     // per SM (k_accumulate_s), or 0 = all-register k_accumulate.  UGB_ACC_G1 / UGB_ACC_G2 override the default.
-    using AccFn = void (*)(const Affine<F>*, const uint32_t*, const uint32_t*, uint32_t, P*, uint32_t*, P*);
+    using AccFn = typename AccSig<F>::Fn;
     const int acc_variant = env_int_msm(g1 ? "UGB_ACC_G1" : "UGB_ACC_G2", g1 ? ACC_VARIANT_G1 : ACC_VARIANT_G2);
     const bool affine = acc_variant >= 20;
     AccFn acc_fn = k_accumulate<F>;
@@ -162,7 +167,7 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     uint64_t want_threads = std::max<uint64_t>(128, (max_entries + 15) / 16);
     uint32_t blocks = (uint32_t)std::min<uint64_t>((uint64_t)ctx.sm_count * occ, (want_threads + 127) / 128);
     uint32_t T = blocks * 128;
-    uint32_t K = 2 * T;
+    uint32_t K = 2 * T * (uint32_t)nb;
     // ping-pong partial lists
     uint32_t* keys_a = (uint32_t*)ctx.workspace("msm.pkeys_a", (size_t)K * 4);
     P* pts_a = (P*)ctx.workspace("msm.ppts_a", (size_t)K * sizeof(P));
@@ -170,16 +175,22 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     uint32_t* keys_b = (uint32_t*)ctx.workspace("msm.pkeys_b", (size_t)K1 * 4);
     P* pts_b = (P*)ctx.workspace("msm.ppts_b", (size_t)K1 * sizeof(P));
 
-    if (affine) {
-        // per-thread scratch lists, sized for the largest possible entry count (the real count is only known on the device)
-        const uint32_t Lmax = (uint32_t)((max_entries + T - 1) / T) + 1;
-        uint4* list_mem = (uint4*)ctx.workspace("msm.ba_list", (size_t)T * Lmax * sizeof(Affine<F>));
-        uint4* suf_mem = (uint4*)ctx.workspace("msm.ba_suf", (size_t)T * (Lmax / 2 + 1) * sizeof(F));
-        uint32_t* keys_mem = (uint32_t*)ctx.workspace("msm.ba_keys", (size_t)T * Lmax * 4);
-        uint32_t* pairs_mem = (uint32_t*)ctx.workspace("msm.ba_pairs", (size_t)T * (Lmax / 2 + 1) * 4);
-        UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), ba_fn<<<blocks, BA_BS, 0, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a, Lmax, list_mem, suf_mem, keys_mem, pairs_mem));
-    } else {
-        UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), acc_fn<<<blocks, 128, acc_smem, ctx.stream>>>(d_bases, dg.entries, dg.starts, cfg.NB, buckets, keys_a, pts_a));
+    for (int m = 0; m < nb; m++) {
+        P* bk = buckets + (size_t)m * cfg.NB;
+        uint32_t* pk = keys_a + (size_t)m * 2 * T;
+        P* pp = pts_a + (size_t)m * 2 * T;
+        const uint32_t key_off = (uint32_t)m * cfg.NB;
+        if (affine) {
+            // per-thread scratch lists, sized for the largest possible entry count (the real count is only known on the device)
+            const uint32_t Lmax = (uint32_t)((max_entries + T - 1) / T) + 1;
+            uint4* list_mem = (uint4*)ctx.workspace("msm.ba_list", (size_t)T * Lmax * sizeof(Affine<F>));
+            uint4* suf_mem = (uint4*)ctx.workspace("msm.ba_suf", (size_t)T * (Lmax / 2 + 1) * sizeof(F));
+            uint32_t* keys_mem = (uint32_t*)ctx.workspace("msm.ba_keys", (size_t)T * Lmax * 4);
+            uint32_t* pairs_mem = (uint32_t*)ctx.workspace("msm.ba_pairs", (size_t)T * (Lmax / 2 + 1) * 4);
+            UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), ba_fn<<<blocks, BA_BS, 0, ctx.stream>>>(d_bases_v[m], dg.entries, dg.starts, cfg.NB, bk, pk, pp, key_off, NBT, Lmax, list_mem, suf_mem, keys_mem, pairs_mem));
+        } else {
+            UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), acc_fn<<<blocks, 128, acc_smem, ctx.stream>>>(d_bases_v[m], dg.entries, dg.starts, cfg.NB, bk, pk, pp, key_off, NBT));
+        }
     }
 
     uint32_t* kin = keys_a; P* pin = pts_a; uint32_t* kout = keys_b; P* pout = pts_b;
@@ -187,7 +198,7 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
     while (true) {
         uint32_t g = (Kcur + SEG_BS - 1) / SEG_BS;
         int final_pass = (g == 1);
-        UG_KERNEL(ctx, (g1 ? "k_seg_reduce<G1>" : "k_seg_reduce<G2>"), k_seg_reduce<F><<<g, SEG_BS, 0, ctx.stream>>>(kin, pin, Kcur, cfg.NB, buckets, kout, pout, final_pass));
+        UG_KERNEL(ctx, (g1 ? "k_seg_reduce<G1>" : "k_seg_reduce<G2>"), k_seg_reduce<F><<<g, SEG_BS, 0, ctx.stream>>>(kin, pin, Kcur, NBT, buckets, kout, pout, final_pass));
         if (final_pass) break;
         Kcur = 2 * g;
         std::swap(kin, kout);
@@ -196,13 +207,14 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
 
     // bucket reduction: one level of chunked running sums, then bit-decomposed plain sums of the chunk sums
     const MsmReducePlan plan = msm_reduce_plan(cfg);
-    const int nwin = cfg.nwin(), L = plan.points();
+    const int nwin1 = cfg.nwin(), L = plan.points();
+    const int nwin = nwin1 * nb;  // bucket sets of the whole batch: window w of MSM m is set m*nwin1 + w
     const uint32_t K0 = plan.K;
     P* S = (P*)ctx.workspace("msm.Sa", (size_t)nwin * K0 * sizeof(P));
     P* R = (P*)ctx.workspace("msm.R", (size_t)nwin * K0 * sizeof(P));
     P* Rpart = (P*)ctx.workspace("msm.Rpart", (size_t)nwin * 64 * 33 * sizeof(P));
-    P* sums = (P*)ctx.workspace("msm.sums." + slot, (size_t)L * nwin * sizeof(P));
-    using RsFn = void (*)(const P*, uint32_t, uint32_t, uint32_t, uint32_t, P*, P*);
+    P* sums = (P*)ctx.workspace("msm.sums", (size_t)L * nwin * sizeof(P));
+    using RsFn = typename RsSig<F>::Fn;
     const int rs_variant = env_int_msm(g1 ? "UGB_RS_G1" : "UGB_RS_G2", g1 ? RS_VARIANT_G1 : RS_VARIANT_G2);
     RsFn rs_fn = k_running_sum<F>;
     size_t rs_smem = 0;
@@ -230,22 +242,31 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* d_bases, const MsmD
             }
         }
     }
-    // pinned result slot: L*nwin partial sums, then the number of digit entries this MSM processed (a counter
-    // for the roofline arithmetic: every entry is one 4-byte index + one affine point gather + one mixed add)
-    const size_t bytes = (size_t)L * nwin * sizeof(P);
-    uint8_t* host = (uint8_t*)ctx.pinned("msm.sums." + slot, (size_t)64 * 32 * sizeof(P) + 16);
+    // pinned result slot per MSM: its L*nwin1 partial sums ([level][window]), then the number of digit entries it processed (a
+    // counter for the roofline arithmetic: every entry is one 4-byte index + one affine point gather + one mixed add)
+    const size_t bytes = (size_t)L * nwin1 * sizeof(P);
     if (bytes > (size_t)64 * 32 * sizeof(P)) throw std::runtime_error("ultragroth_b200: MSM reduction plan too deep");
-    UG_CUDA_CHECK(cudaMemcpyAsync(host, sums, bytes, cudaMemcpyDeviceToHost, ctx.stream));
-    UG_CUDA_CHECK(cudaMemcpyAsync(host + bytes, dg.starts + cfg.NB, 4, cudaMemcpyDeviceToHost, ctx.stream));
-    ctx.record("msm." + slot);
+    for (int m = 0; m < nb; m++) {
+        uint8_t* host = (uint8_t*)ctx.pinned("msm.sums." + slots[m], (size_t)64 * 32 * sizeof(P) + 16);
+        UG_CUDA_CHECK(cudaMemcpy2DAsync(host, (size_t)nwin1 * sizeof(P), sums + (size_t)m * nwin1, (size_t)nwin * sizeof(P),
+                                        (size_t)nwin1 * sizeof(P), (size_t)L, cudaMemcpyDeviceToHost, ctx.stream));
+        UG_CUDA_CHECK(cudaMemcpyAsync(host + bytes, dg.starts + cfg.NB, 4, cudaMemcpyDeviceToHost, ctx.stream));
+    }
+    for (int m = 0; m < nb; m++) ctx.record("msm." + slots[m]);
 }
 
 void msm_g1_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot) {
-    msm_launch_impl<Fq>(ctx, (const G1Affine*)d_bases, dg, slot);
+    const G1Affine* b = (const G1Affine*)d_bases;
+    msm_launch_impl<Fq>(ctx, &b, 1, dg, &slot);
+}
+void msm_g1_launch_batch(DeviceCtx& ctx, const void* const* d_bases, int count, const MsmDigits& dg, const std::string* slots) {
+    if (count < 1 || count > 8) throw std::invalid_argument("ultragroth_b200: MSM batch of 1..8 base arrays");
+    msm_launch_impl<Fq>(ctx, (const G1Affine* const*)d_bases, count, dg, slots);
 }
 void msm_g2_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot) {
     // every G2 kernel is instantiated on Fq2c (Fq2's layout, CALLED products): an inlined Fq2 kernel is 200-500 KB of SASS
-    msm_launch_impl<Fq2c>(ctx, (const Affine<Fq2c>*)d_bases, dg, slot);
+    const Affine<Fq2c>* b = (const Affine<Fq2c>*)d_bases;
+    msm_launch_impl<Fq2c>(ctx, &b, 1, dg, &slot);
 }
 
 // ---- resident window tables ----------------------------------------------------------------------

@@ -178,19 +178,20 @@ __global__ void __launch_bounds__(SCAN_BS) k_scan_apply(const uint32_t* __restri
 // ---- bucket accumulation ----------------------------------------------------------------------
 // starts[0..NB] = bucket offsets into entries (starts[NB] = total M).  Thread t owns entries
 // [t*L, (t+1)*L), L = ceil(M/T).  Outputs: buckets[key] for runs strictly inside the slice,
-// (pkeys, ppts)[2t], [2t+1] for the first and last run of the slice.
+// (pkeys, ppts)[2t], [2t+1] for the first and last run of the slice.  key_off / key_none: several MSMs that share one digit sort
+// are reduced together (msm.cu: batch): pkeys carry key + key_off (position in the concatenated bucket array), key_none = "no run".
 template <class F>
 __global__ void __launch_bounds__(128) k_accumulate(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
                                                     const uint32_t* __restrict__ starts, uint32_t NB,
                                                     XYZZ<F>* __restrict__ buckets, uint32_t* __restrict__ pkeys,
-                                                    XYZZ<F>* __restrict__ ppts) {
+                                                    XYZZ<F>* __restrict__ ppts, uint32_t key_off, uint32_t key_none) {
     const uint32_t T = gridDim.x * blockDim.x;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t M = starts[NB];
     const uint32_t L = (uint32_t)(((uint64_t)M + T - 1) / T);
     const uint64_t lo64 = (uint64_t)t * L;
     if (L == 0 || lo64 >= M) {
-        pkeys[2 * t] = NB; pkeys[2 * t + 1] = NB;
+        pkeys[2 * t] = key_none; pkeys[2 * t + 1] = key_none;
         st_g(&ppts[2 * t], XYZZ<F>::inf());
         st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
         return;
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(128) k_accumulate(const Affine<F>* __restrict_
     Affine<F> pt = ld_nc(&bases[e & 0x7fffffffu]);
     for (uint32_t pos = lo; pos < hi; pos++) {
         if (pos == end) {
-            if (first) { pkeys[2 * t] = key; st_g(&ppts[2 * t], acc); first = false; }
+            if (first) { pkeys[2 * t] = key + key_off; st_g(&ppts[2 * t], acc); first = false; }
             else st_g(&buckets[key], acc);
             acc = XYZZ<F>::inf();
             do { key++; end = starts[key + 1]; } while (end <= pos);
@@ -225,10 +226,10 @@ __global__ void __launch_bounds__(128) k_accumulate(const Affine<F>* __restrict_
         if (has_next) { e = e_next; pt = pt_next; }
     }
     if (first) {
-        pkeys[2 * t] = key; st_g(&ppts[2 * t], acc);
-        pkeys[2 * t + 1] = key; st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
+        pkeys[2 * t] = key + key_off; st_g(&ppts[2 * t], acc);
+        pkeys[2 * t + 1] = key + key_off; st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
     } else {
-        pkeys[2 * t + 1] = key; st_g(&ppts[2 * t + 1], acc);
+        pkeys[2 * t + 1] = key + key_off; st_g(&ppts[2 * t + 1], acc);
     }
 }
 
@@ -238,7 +239,7 @@ template <class F, int MINB>
 __global__ void __launch_bounds__(128, MINB) k_accumulate_s(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
                                                             const uint32_t* __restrict__ starts, uint32_t NB,
                                                             XYZZ<F>* __restrict__ buckets, uint32_t* __restrict__ pkeys,
-                                                            XYZZ<F>* __restrict__ ppts) {
+                                                            XYZZ<F>* __restrict__ ppts, uint32_t key_off, uint32_t key_none) {
     extern __shared__ uint4 slab[];
     const SmemPoint<F, 128> acc{slab + threadIdx.x};
     const uint32_t T = gridDim.x * blockDim.x;
@@ -247,7 +248,7 @@ __global__ void __launch_bounds__(128, MINB) k_accumulate_s(const Affine<F>* __r
     const uint32_t L = (uint32_t)(((uint64_t)M + T - 1) / T);
     const uint64_t lo64 = (uint64_t)t * L;
     if (L == 0 || lo64 >= M) {
-        pkeys[2 * t] = NB; pkeys[2 * t + 1] = NB;
+        pkeys[2 * t] = key_none; pkeys[2 * t + 1] = key_none;
         st_g(&ppts[2 * t], XYZZ<F>::inf());
         st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
         return;
@@ -267,7 +268,7 @@ __global__ void __launch_bounds__(128, MINB) k_accumulate_s(const Affine<F>* __r
     Affine<F> pt = ld_nc(&bases[e & 0x7fffffffu]);
     for (uint32_t pos = lo; pos < hi; pos++) {
         if (pos == end) {
-            if (first) { pkeys[2 * t] = key; st_g(&ppts[2 * t], acc.get()); first = false; }
+            if (first) { pkeys[2 * t] = key + key_off; st_g(&ppts[2 * t], acc.get()); first = false; }
             else st_g(&buckets[key], acc.get());
             acc.set_inf();
             do { key++; end = starts[key + 1]; } while (end <= pos);
@@ -278,10 +279,10 @@ __global__ void __launch_bounds__(128, MINB) k_accumulate_s(const Affine<F>* __r
         pt_madd_at<F>(acc, cur, neg);
     }
     if (first) {
-        pkeys[2 * t] = key; st_g(&ppts[2 * t], acc.get());
-        pkeys[2 * t + 1] = key; st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
+        pkeys[2 * t] = key + key_off; st_g(&ppts[2 * t], acc.get());
+        pkeys[2 * t + 1] = key + key_off; st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
     } else {
-        pkeys[2 * t + 1] = key; st_g(&ppts[2 * t + 1], acc.get());
+        pkeys[2 * t + 1] = key + key_off; st_g(&ppts[2 * t + 1], acc.get());
     }
 }
 
@@ -381,7 +382,8 @@ template <class F, int MINB>
 __global__ void __launch_bounds__(BA_BS, MINB) k_accumulate_affine(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
                                                                    const uint32_t* __restrict__ starts, uint32_t NB,
                                                                    XYZZ<F>* __restrict__ buckets, uint32_t* __restrict__ pkeys,
-                                                                   XYZZ<F>* __restrict__ ppts, uint32_t Lmax, uint4* __restrict__ list_mem,
+                                                                   XYZZ<F>* __restrict__ ppts, uint32_t key_off, uint32_t key_none,
+                                                                   uint32_t Lmax, uint4* __restrict__ list_mem,
                                                                    uint4* __restrict__ suf_mem, uint32_t* __restrict__ keys_mem,
                                                                    uint32_t* __restrict__ pairs_mem) {
     __shared__ F tree[2 * BA_BS];
@@ -479,7 +481,7 @@ __global__ void __launch_bounds__(BA_BS, MINB) k_accumulate_affine(const Affine<
 
     // one point per run: interior runs are complete buckets, the first and last run may continue in a neighbour's slice
     if (n == 0) {
-        pkeys[2 * t] = NB; pkeys[2 * t + 1] = NB;
+        pkeys[2 * t] = key_none; pkeys[2 * t + 1] = key_none;
         st_g(&ppts[2 * t], XYZZ<F>::inf());
         st_g(&ppts[2 * t + 1], XYZZ<F>::inf());
         return;
@@ -487,11 +489,11 @@ __global__ void __launch_bounds__(BA_BS, MINB) k_accumulate_affine(const Affine<
     for (uint32_t i = 0; i < n; i++) {
         const uint32_t key = K[(size_t)i * BA_BS];
         const XYZZ<F> v = XYZZ<F>::from_affine(list.ld(i));
-        if (i == 0) { pkeys[2 * t] = key; st_g(&ppts[2 * t], v); }
-        else if (i == n - 1) { pkeys[2 * t + 1] = key; st_g(&ppts[2 * t + 1], v); }
+        if (i == 0) { pkeys[2 * t] = key + key_off; st_g(&ppts[2 * t], v); }
+        else if (i == n - 1) { pkeys[2 * t + 1] = key + key_off; st_g(&ppts[2 * t + 1], v); }
         else st_g(&buckets[key], v);
     }
-    if (n == 1) { pkeys[2 * t + 1] = K[0]; st_g(&ppts[2 * t + 1], XYZZ<F>::inf()); }
+    if (n == 1) { pkeys[2 * t + 1] = K[0] + key_off; st_g(&ppts[2 * t + 1], XYZZ<F>::inf()); }
 }
 
 // ---- segmented reduction of (key, point) pairs sorted by key -----------------------------------

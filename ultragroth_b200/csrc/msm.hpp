@@ -73,6 +73,8 @@ void msm_accumulate_g2(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg,
 // when the digits were sorted for that table.
 void msm_g1_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot);
 void msm_g1_finish(DeviceCtx& ctx, const MsmDigits& dg, const std::string& slot, HG1XYZZ* out);
+// `count` base arrays (tables) that pair with the same digits: separate accumulations, ONE shared reduction tail; finish per slot
+void msm_g1_launch_batch(DeviceCtx& ctx, const void* const* d_bases, int count, const MsmDigits& dg, const std::string* slots);
 void msm_g2_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot);
 void msm_g2_finish(DeviceCtx& ctx, const MsmDigits& dg, const std::string& slot, HG2XYZZ* out);
 
