@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(SCAN_BS) k_scan_apply(const uint32_t* __restri
 // (pkeys, ppts)[2t], [2t+1] for the first and last run of the slice.  key_off / key_none: several MSMs that share one digit sort
 // are reduced together (msm.cu: batch): pkeys carry key + key_off (position in the concatenated bucket array), key_none = "no run".
 template <class F>
-__global__ void __launch_bounds__(128) k_accumulate(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
+__global__ void __launch_bounds__(128, sizeof(F) == 32 ? 4 : 1) k_accumulate(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
                                                     const uint32_t* __restrict__ starts, uint32_t NB,
                                                     XYZZ<F>* __restrict__ buckets, uint32_t* __restrict__ pkeys,
                                                     XYZZ<F>* __restrict__ ppts, uint32_t key_off, uint32_t key_none) {

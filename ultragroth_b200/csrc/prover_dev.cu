@@ -370,7 +370,8 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     msm_sort_digits(ctx, (const uint8_t*)w_ + w_lo_ * 32, nullptr, w_hi_ - w_lo_, 0, "w", dw, pre_ ? &cfg_w_ : nullptr);
     mark();  // 1
     MsmDigits dc;
-    if (c_shares_witness_sort_) {
+    static const bool batch_abc = !(getenv("UGB_MSM_BATCH") && atoi(getenv("UGB_MSM_BATCH")) == 0);
+    if (c_shares_witness_sort_ && batch_abc) {
         // A, B1 and C multiply the same witness: one shared reduction tail (msm_g1_launch_batch); the stage clock is split evenly
         const void* bases[3] = {A_, B1_, C_};
         const std::string slots[3] = {"a", "b1", "c"};
@@ -386,8 +387,12 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
         mark();  // 3
         msm_g2_launch(ctx, B2_, dw, "b2");
         mark();  // 4
-        msm_sort_digits(ctx, (const uint8_t*)w_, idx_c2_, n_c2_, 0, "cidx", dc, pre_ ? &cfg_c2_ : nullptr);
-        msm_g1_launch(ctx, C_, dc, "c");
+        if (c_shares_witness_sort_) {
+            msm_g1_launch(ctx, C_, dw, "c");
+        } else {
+            msm_sort_digits(ctx, (const uint8_t*)w_, idx_c2_, n_c2_, 0, "cidx", dc, pre_ ? &cfg_c2_ : nullptr);
+            msm_g1_launch(ctx, C_, dc, "c");
+        }
     }
     mark();  // 5
     // H pipeline
@@ -423,7 +428,7 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
         float* dst[] = {&last_times.sort_w, &last_times.msm_a, &last_times.msm_b1, &last_times.msm_b2, &last_times.msm_c, &last_times.spmv,
                         &last_times.intt, &last_times.ntt, &last_times.hfinal, &last_times.sort_h, &last_times.msm_h};
         for (int i = 0; i < 11; i++) UG_CUDA_CHECK(cudaEventElapsedTime(dst[i], ev_[i], ev_[i + 1]));
-        if (c_shares_witness_sort_) {  // the batched A/B1/C launch was timed as one interval (recorded under msm_a)
+        if (c_shares_witness_sort_ && batch_abc) {  // the batched A/B1/C launch was timed as one interval (recorded under msm_a)
             const float each = last_times.msm_a / 3.0f;
             last_times.msm_a = last_times.msm_b1 = last_times.msm_c = each;
         }
