@@ -131,7 +131,8 @@ int ugb_ultra_prove_assemble(void* prover_object, const void* partials, uint32_t
 
 /* ---- microbenchmarks for the roofline denominators ----
  * kind 0: independent 32-bit IMAD chains; 1: IMAD.WIDE (mad.wide.u32) chains; 2: dependent Fq Montgomery
- * products (4 chains per thread).  Returns operations per second in *ops_per_s. */
+ * products (4 chains per thread); 3 / 4: IMAD.WIDE rows with carry-in+out / carry-out only; 5: kind 2 on the Karatsuba product
+ * fp_mul_ks.  Returns operations per second in *ops_per_s. */
 int ugb_bench_int_pipe(ugb_ctx* ctx, int kind, double* ops_per_s);
 
 /* ---- harness tooling: synthetic circuits with a VALID trusted setup ----

@@ -239,3 +239,36 @@ def test_oracle_reproduces_golden_testdata_proof():
     assert hashlib.sha256(b"".join(int(x).to_bytes(32, "little") for x in inter["h"])).hexdigest() == g["h_sha256"]
     vkj = open(os.path.join(gold, "ref_testdata", "verification_key.json")).read()
     assert uv.groth16_verify(json.dumps(g["proof"]), json.dumps(g["public"]), vkj) == (uv.VERIFIER_VALID_PROOF, "")
+
+
+def test_karatsuba_product_matches_cios_product_on_cpu(tmp_path):
+    """fp_mul_ks (Karatsuba + separate Montgomery reduction, ff.cuh) against fp_mul -- itself pinned to the reference's field code
+    above -- on 2*10^5 random and edge-case operand pairs per field, through the host build of the device limb code."""
+    import subprocess
+    src = tmp_path / "ks.cpp"
+    src.write_text(r'''
+#include "ff.cuh"
+#include <cstdio>
+#include <cstdlib>
+using namespace ug;
+template <class F> int run() {
+    srand(7);
+    int bad = 0;
+    for (int it = 0; it < 200000; it++) {
+        F x, y;
+        for (int i = 0; i < 8; i++) { x.v[i] = (uint32_t)rand() * 65537u + (uint32_t)rand(); y.v[i] = (uint32_t)rand() * 65537u + (uint32_t)rand(); }
+        if (it % 7 == 0) for (int i = 0; i < 8; i++) x.v[i] = 0xffffffffu;
+        if (it % 11 == 0) { y = F::modulus(); y.v[0] -= 1; } else { y.v[7] &= 0x1fffffffu; }
+        if (it % 13 == 0) for (int i = 0; i < 4; i++) { x.v[i] = x.v[i + 4] = 0xffffffffu; y.v[i] = 0xffffffffu; y.v[4 + i] = (i == 3) ? 0x1fffffffu : 0xffffffffu; }
+        if (it % 17 == 0) x = F::zero();
+        if (!(fp_mul(x, y) == fp_mul_ks(x, y))) bad++;
+    }
+    return bad;
+}
+int main() { int b = run<Fq>() + run<Fr>(); printf("mismatches %d\n", b); return b != 0; }
+''')
+    exe = tmp_path / "ks"
+    root = os.path.dirname(HERE)
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-I", os.path.join(root, "ultragroth_b200", "csrc"), str(src), "-o", str(exe)])
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0 and "mismatches 0" in out.stdout, out.stdout + out.stderr

@@ -40,6 +40,10 @@ UG_D uint32_t subc_cc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("subc.c
 UG_D uint32_t subc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("subc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
 UG_D uint32_t mul_lo(uint32_t a, uint32_t b) { uint32_t r; asm volatile("mul.lo.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
 UG_D uint32_t mul_hi(uint32_t a, uint32_t b) { uint32_t r; asm volatile("mul.hi.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+// full 32x32 -> 64 product in ONE IMAD.WIDE (mul.lo + mul.hi would be an IMAD and an IMAD.HI)
+UG_D void mul_wide(uint32_t a, uint32_t b, uint32_t& lo, uint32_t& hi) {
+    asm volatile("{\n\t.reg .u64 t;\n\tmul.wide.u32 t, %2, %3;\n\tmov.b64 {%0, %1}, t;\n\t}" : "=r"(lo), "=r"(hi) : "r"(a), "r"(b));
+}
 UG_D uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("mad.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
 UG_D uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
 UG_D uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.hi.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
@@ -55,6 +59,7 @@ inline uint32_t subc_cc(uint32_t a, uint32_t b) { uint64_t s = (uint64_t)a - b -
 inline uint32_t subc(uint32_t a, uint32_t b) { return a - b - g_cc; }
 inline uint32_t mul_lo(uint32_t a, uint32_t b) { return a * b; }
 inline uint32_t mul_hi(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * b) >> 32); }
+inline void mul_wide(uint32_t a, uint32_t b, uint32_t& lo, uint32_t& hi) { uint64_t p = (uint64_t)a * b; lo = (uint32_t)p; hi = (uint32_t)(p >> 32); }
 inline uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { return add_cc(a * b, c); }
 inline uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { return addc_cc(a * b, c); }
 inline uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { return addc_cc(mul_hi(a, b), c); }
@@ -205,7 +210,7 @@ UG_HD void mont_reduce_row(uint32_t* a0, uint32_t* a1) {
     a1[4] = madc_lo_cc(P::mod(5), m, a1[4]);
     a1[5] = madc_hi_cc(P::mod(5), m, a1[5]);
     a1[6] = madc_lo_cc(P::mod(7), m, a1[6]);
-    a1[7] = madc_hi(P::mod(7), m, a1[7]);
+    a1[7] = madc_hi_cc(P::mod(7), m, a1[7]);  // carry out is impossible (value < 2^32 * 2p); .cc only so that ptxas fuses the pair
     a0[0] = mad_lo_cc(P::mod(0), m, a0[0]);
     a0[1] = madc_hi_cc(P::mod(0), m, a0[1]);
     a0[2] = madc_lo_cc(P::mod(2), m, a0[2]);
@@ -230,7 +235,7 @@ UG_HD void mont_mul_row(uint32_t* prev0, uint32_t* prev1, const uint32_t* y, uin
     prev0[4] = madc_lo_cc(y[5], x, prev0[6]);
     prev0[5] = madc_hi_cc(y[5], x, prev0[7]);
     prev0[6] = madc_lo_cc(y[7], x, 0);
-    prev0[7] = madc_hi(y[7], x, 0);
+    prev0[7] = madc_hi_cc(y[7], x, 0);
     prev1[0] = mad_lo_cc(y[0], x, prev1[0]);
     prev1[1] = madc_hi_cc(y[0], x, prev1[1]);
     prev1[2] = madc_lo_cc(y[2], x, prev1[2]);
@@ -252,10 +257,8 @@ UG_HD Fp<P> fp_mul(const Fp<P>& x, const Fp<P>& y) {
         uint32_t x0 = x.v[0];
 #pragma unroll
         for (int k = 0; k < 8; k += 2) {
-            e[k] = mul_lo(y.v[k], x0);
-            e[k + 1] = mul_hi(y.v[k], x0);
-            o[k] = mul_lo(y.v[k + 1], x0);
-            o[k + 1] = mul_hi(y.v[k + 1], x0);
+            mul_wide(y.v[k], x0, e[k], e[k + 1]);
+            mul_wide(y.v[k + 1], x0, o[k], o[k + 1]);
         }
         mont_reduce_row<P>(e, o);
     }
@@ -270,6 +273,129 @@ UG_HD Fp<P> fp_mul(const Fp<P>& x, const Fp<P>& y) {
 #pragma unroll
     for (int k = 1; k < 7; k++) r.v[k] = addc_cc(e[k], o[k + 1]);
     r.v[7] = addc(e[7], 0);
+    fp_final_sub(r);
+    return r;
+}
+
+// ---- product-scanning variant: one Karatsuba level + separate Montgomery reduction ------------------------------
+// fp_mul spends 64 of its 136 wide multiply-adds on x*y.  Splitting both operands in 128-bit halves needs three 4x4-limb
+// products (48) and ~100 additions, which run on the ALU pipe that the bucket kernels leave 75 % idle; the 8 reduction rows
+// (64 + 8) are unchanged.  Same value as fp_mul for every input with y < p (checked against the reference's field code
+// through tests/emul on the CPU and the GPU parity tests).  UG_FP_MUL_KARATSUBA selects it for Fq (curve arithmetic).
+
+// r[0..7] = a[0..3] * b[0..3].  Even-start limb pairs accumulate in ev (positions 0..7), odd-start pairs in od (positions
+// 1..7), so that every (mad.lo.cc, madc.hi.cc) pair is an aligned IMAD.WIDE; the carry out of a row lands on a limb that
+// holds at most earlier carries, so a plain addc ends the chain.
+UG_HD void mul4x4(const uint32_t* a, const uint32_t* b, uint32_t* r) {
+    uint32_t ev[8], od[7];
+    // row 0 (x = b0): a0,a2 -> ev pairs (0,1),(2,3); a1,a3 -> od pairs (1,2),(3,4)
+    mul_wide(a[0], b[0], ev[0], ev[1]);
+    mul_wide(a[2], b[0], ev[2], ev[3]);
+    mul_wide(a[1], b[0], od[0], od[1]);
+    mul_wide(a[3], b[0], od[2], od[3]);
+    // row 1 (x = b1): a0,a2 -> od pairs (1,2),(3,4), carry -> position 5; a1,a3 -> ev pairs (2,3),(4,5), carry -> 6
+    od[0] = mad_lo_cc(a[0], b[1], od[0]); od[1] = madc_hi_cc(a[0], b[1], od[1]);
+    od[2] = madc_lo_cc(a[2], b[1], od[2]); od[3] = madc_hi_cc(a[2], b[1], od[3]);
+    od[4] = addc(0, 0);
+    ev[2] = mad_lo_cc(a[1], b[1], ev[2]); ev[3] = madc_hi_cc(a[1], b[1], ev[3]);
+    ev[4] = madc_lo_cc(a[3], b[1], 0); ev[5] = madc_hi_cc(a[3], b[1], 0);
+    ev[6] = addc(0, 0);
+    // row 2 (x = b2): a0,a2 -> ev pairs (2,3),(4,5), carry -> 6; a1,a3 -> od pairs (3,4),(5,6), carry -> 7
+    ev[2] = mad_lo_cc(a[0], b[2], ev[2]); ev[3] = madc_hi_cc(a[0], b[2], ev[3]);
+    ev[4] = madc_lo_cc(a[2], b[2], ev[4]); ev[5] = madc_hi_cc(a[2], b[2], ev[5]);
+    ev[6] = addc(ev[6], 0);
+    od[2] = mad_lo_cc(a[1], b[2], od[2]); od[3] = madc_hi_cc(a[1], b[2], od[3]);
+    od[4] = madc_lo_cc(a[3], b[2], od[4]); od[5] = madc_hi_cc(a[3], b[2], 0);
+    od[6] = addc(0, 0);
+    // row 3 (x = b3): a0,a2 -> od pairs (3,4),(5,6), carry -> 7; a1,a3 -> ev pairs (4,5),(6,7)
+    od[2] = mad_lo_cc(a[0], b[3], od[2]); od[3] = madc_hi_cc(a[0], b[3], od[3]);
+    od[4] = madc_lo_cc(a[2], b[3], od[4]); od[5] = madc_hi_cc(a[2], b[3], od[5]);
+    od[6] = addc(od[6], 0);
+    ev[4] = mad_lo_cc(a[1], b[3], ev[4]); ev[5] = madc_hi_cc(a[1], b[3], ev[5]);
+    ev[6] = madc_lo_cc(a[3], b[3], ev[6]); ev[7] = madc_hi_cc(a[3], b[3], 0);
+    // r = ev + (od << 32)
+    r[0] = ev[0];
+    r[1] = add_cc(ev[1], od[0]);
+#pragma unroll
+    for (int k = 2; k < 7; k++) r[k] = addc_cc(ev[k], od[k - 1]);
+    r[7] = addc(ev[7], od[6]);
+}
+
+// one fused "shift by a limb, bring in the next limb of T, reduce" row of the separate reduction: prev0 is the old column-0
+// accumulator (prev0[0] == 0), prev1 the old column-1 accumulator; afterwards prev1 is column 0 (prev1[0] == 0), prev0 column 1
+template <class P>
+UG_HD void mont_sos_row(uint32_t* prev0, uint32_t* prev1, uint32_t tnext) {
+    prev1[0] = add_cc(prev1[0], prev0[1]);
+    const uint32_t m = mul_lo(prev1[0], P::NP0);
+    prev0[0] = madc_lo_cc(P::mod(1), m, prev0[2]);
+    prev0[1] = madc_hi_cc(P::mod(1), m, prev0[3]);
+    prev0[2] = madc_lo_cc(P::mod(3), m, prev0[4]);
+    prev0[3] = madc_hi_cc(P::mod(3), m, prev0[5]);
+    prev0[4] = madc_lo_cc(P::mod(5), m, prev0[6]);
+    prev0[5] = madc_hi_cc(P::mod(5), m, prev0[7]);
+    prev0[6] = madc_lo_cc(P::mod(7), m, tnext);
+    prev0[7] = madc_hi_cc(P::mod(7), m, 0);
+    prev1[0] = mad_lo_cc(P::mod(0), m, prev1[0]);
+    prev1[1] = madc_hi_cc(P::mod(0), m, prev1[1]);
+    prev1[2] = madc_lo_cc(P::mod(2), m, prev1[2]);
+    prev1[3] = madc_hi_cc(P::mod(2), m, prev1[3]);
+    prev1[4] = madc_lo_cc(P::mod(4), m, prev1[4]);
+    prev1[5] = madc_hi_cc(P::mod(4), m, prev1[5]);
+    prev1[6] = madc_lo_cc(P::mod(6), m, prev1[6]);
+    prev1[7] = madc_hi_cc(P::mod(6), m, prev1[7]);
+    prev0[7] = addc(prev0[7], 0);
+}
+
+template <class P>
+UG_HD Fp<P> fp_mul_ks(const Fp<P>& x, const Fp<P>& y) {
+    uint32_t T[16];
+    {
+        uint32_t zm[9], sa[4], sb[4];
+        mul4x4(x.v, y.v, T);            // z0 = x_lo * y_lo
+        mul4x4(x.v + 4, y.v + 4, T + 8);  // z2 = x_hi * y_hi
+        sa[0] = add_cc(x.v[0], x.v[4]); sa[1] = addc_cc(x.v[1], x.v[5]); sa[2] = addc_cc(x.v[2], x.v[6]); sa[3] = addc_cc(x.v[3], x.v[7]);
+        const uint32_t ca = 0u - addc(0, 0);  // all ones when x_lo + x_hi overflowed 128 bits
+        sb[0] = add_cc(y.v[0], y.v[4]); sb[1] = addc_cc(y.v[1], y.v[5]); sb[2] = addc_cc(y.v[2], y.v[6]); sb[3] = addc_cc(y.v[3], y.v[7]);
+        const uint32_t cb = 0u - addc(0, 0);
+        mul4x4(sa, sb, zm);
+        // (sa + ca*2^128) * (sb + cb*2^128) = sa*sb + 2^128 * (ca*sb + cb*sa) + 2^256 * (ca & cb)
+        zm[4] = add_cc(zm[4], sb[0] & ca); zm[5] = addc_cc(zm[5], sb[1] & ca); zm[6] = addc_cc(zm[6], sb[2] & ca); zm[7] = addc_cc(zm[7], sb[3] & ca);
+        zm[8] = addc(ca & cb & 1u, 0);
+        zm[4] = add_cc(zm[4], sa[0] & cb); zm[5] = addc_cc(zm[5], sa[1] & cb); zm[6] = addc_cc(zm[6], sa[2] & cb); zm[7] = addc_cc(zm[7], sa[3] & cb);
+        zm[8] = addc(zm[8], 0);
+        // z1 = zm - z0 - z2  (>= 0, < 2^258)
+        zm[0] = sub_cc(zm[0], T[0]);
+#pragma unroll
+        for (int k = 1; k < 8; k++) zm[k] = subc_cc(zm[k], T[k]);
+        zm[8] = subc(zm[8], 0);
+        zm[0] = sub_cc(zm[0], T[8]);
+#pragma unroll
+        for (int k = 1; k < 8; k++) zm[k] = subc_cc(zm[k], T[8 + k]);
+        zm[8] = subc(zm[8], 0);
+        // T += z1 << 128
+        T[4] = add_cc(T[4], zm[0]);
+#pragma unroll
+        for (int k = 1; k < 9; k++) T[4 + k] = addc_cc(T[4 + k], zm[k]);
+        T[13] = addc_cc(T[13], 0); T[14] = addc_cc(T[14], 0); T[15] = addc(T[15], 0);
+    }
+    // separate Montgomery reduction: the 9-limb window starts as T[0..7]; after every row it moves up one limb and the next
+    // limb of T enters at window position 7 (T[15] is added with the final fold)
+    uint32_t e[8], o[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { e[k] = T[k]; o[k] = 0; }
+    mont_reduce_row<P>(e, o);
+    mont_sos_row<P>(e, o, T[8]);   // o column 0, e column 1
+    mont_sos_row<P>(o, e, T[9]);   // e column 0, o column 1
+    mont_sos_row<P>(e, o, T[10]);
+    mont_sos_row<P>(o, e, T[11]);
+    mont_sos_row<P>(e, o, T[12]);
+    mont_sos_row<P>(o, e, T[13]);
+    mont_sos_row<P>(e, o, T[14]);  // o column 0 (o[0] == 0), e column 1
+    Fp<P> r;
+    r.v[0] = add_cc(e[0], o[1]);
+#pragma unroll
+    for (int k = 1; k < 7; k++) r.v[k] = addc_cc(e[k], o[k + 1]);
+    r.v[7] = addc(e[7], T[15]);
     fp_final_sub(r);
     return r;
 }
