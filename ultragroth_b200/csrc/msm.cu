@@ -49,6 +49,8 @@ MsmReducePlan msm_reduce_plan(const MsmConfig& cfg) {
     uint64_t total = (uint64_t)cfg.B * cfg.nwin();
     int mu = 2;
     while (mu < 8 && (total >> mu) > 65536) mu++;
+    const int forced = env_int_msm("UGB_RS_MU", 0);  // experiment knob: chunk = 2^mu buckets
+    if (forced >= 1 && forced <= 10) mu = forced;
     p.mu = mu;
     p.K = (cfg.B + (1u << mu) - 1) >> mu;
     p.nbits = 0;
