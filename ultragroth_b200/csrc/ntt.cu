@@ -120,7 +120,7 @@ static int env_int(const char* name, int dflt) {
 
 // Splits log2(n) into passes of at most `maxT` stage bits over tiles of at most 2^logE elements.
 static std::vector<PassShape> ntt_schedule(int logn) {
-    const int logE = std::min(std::max(env_int("UGB_NTT_LOGE", 12), 6), 12);  // tile elements (2^12 = 128 KiB)
+    const int logE = std::min(std::max(env_int("UGB_NTT_LOGE", 11), 6), 12);  // tile elements (2^11 = 64 KiB: 3 CTAs per SM overlap load/store with butterflies)
     std::vector<PassShape> passes;  // ordered from the low bits up
     if (logn <= logE) {
         passes.push_back({0, logn, 0});
@@ -166,7 +166,7 @@ void ntt_run(DeviceCtx& ctx, NttTables& tabs, Fr* const* d_vecs, int count, int 
     if (dif) std::reverse(sched.begin(), sched.end());  // DIF starts at the high bits
     const Fr* S = tabs.stage_roots(inverse);
     const Fr* W = sched.size() > 1 ? tabs.full_roots(logn) : nullptr;
-    const int threads = std::min(std::max(env_int("UGB_NTT_THREADS", 512), 32), 1024);
+    const int threads = std::min(std::max(env_int("UGB_NTT_THREADS", 256), 32), 1024);
     for (size_t k = 0; k < sched.size(); k++) {
         const PassShape& ps = sched[k];
         NttPass a;
