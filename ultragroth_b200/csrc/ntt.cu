@@ -130,6 +130,8 @@ static std::vector<PassShape> ntt_schedule(int logn) {
     if (npass < 2) npass = 2;
     // strided passes want >= 4 contiguous columns (128 B); if 2 passes cannot give that, use 3
     const int minLogC = std::min(std::max(env_int("UGB_NTT_MIN_LOGC", 1), 0), 4);
+    // ... and no more than 2^maxLogC: once the pass count is fixed, smaller tiles (more CTAs per SM) hide barriers better
+    const int maxLogC = std::min(std::max(env_int("UGB_NTT_MAX_LOGC", 1), minLogC), 11);
     while (true) {
         int base = logn / npass, rem = logn % npass;
         bool ok = true;
@@ -139,6 +141,7 @@ static std::vector<PassShape> ntt_schedule(int logn) {
             int T = base + (i < rem ? 1 : 0);  // low passes take the larger share (they are contiguous)
             int logC = (i == 0) ? 0 : std::min(lo, logE - T);
             if (i > 0 && logC < std::min(minLogC, lo)) ok = false;
+            logC = std::min(logC, maxLogC);
             out.push_back({lo, T, logC});
             lo += T;
         }
@@ -166,7 +169,7 @@ void ntt_run(DeviceCtx& ctx, NttTables& tabs, Fr* const* d_vecs, int count, int 
     if (dif) std::reverse(sched.begin(), sched.end());  // DIF starts at the high bits
     const Fr* S = tabs.stage_roots(inverse);
     const Fr* W = sched.size() > 1 ? tabs.full_roots(logn) : nullptr;
-    const int threads = std::min(std::max(env_int("UGB_NTT_THREADS", 256), 32), 1024);
+    const int threads_env = env_int("UGB_NTT_THREADS", 0);  // 0: one thread per 8 tile elements, 128..256
     for (size_t k = 0; k < sched.size(); k++) {
         const PassShape& ps = sched[k];
         NttPass a;
@@ -188,6 +191,7 @@ void ntt_run(DeviceCtx& ctx, NttTables& tabs, Fr* const* d_vecs, int count, int 
         const uint32_t E = 1u << (ps.T + ps.logC);
         const uint32_t tiles = (1u << logn) / E;
         const size_t smem = (size_t)E * 32;
+        const int threads = threads_env > 0 ? std::min(std::max(threads_env, 32), 1024) : (int)std::min<uint32_t>(std::max<uint32_t>(E / 8, 128), 256);
         const int bt = (int)std::min<uint32_t>(threads, std::max<uint32_t>(32, E / 2));
         dim3 grid(tiles, count);
         const char* kname = dif ? (ps.lo ? "k_ntt_pass<dif,strided>" : "k_ntt_pass<dif,contig>")
