@@ -80,3 +80,35 @@ def test_ntt_large_properties(ctx, logn):
     assert x0 == total
     ctx.ntt(d, logn, inverse=True)
     assert ctx.download(d) == raw.tobytes()
+
+
+SCHEDULES = [
+    {"UGB_NTT_LOGE": "12", "UGB_NTT_MAX_LOGC": "11", "UGB_NTT_THREADS": "512"},   # one 128 KiB tile per SM (the first design)
+    {"UGB_NTT_LOGE": "6", "UGB_NTT_MIN_LOGC": "0", "UGB_NTT_THREADS": "32"},      # 64-element tiles: 3 passes at 2^13
+    {"UGB_NTT_LOGE": "7", "UGB_NTT_MIN_LOGC": "3", "UGB_NTT_MAX_LOGC": "4"},      # forces an extra pass for wide columns
+    {"UGB_NTT_LOGE": "11", "UGB_NTT_MIN_LOGC": "0", "UGB_NTT_MAX_LOGC": "0"},     # single-column strided tiles
+]
+
+
+@pytest.mark.parametrize("sched", SCHEDULES, ids=lambda s: "-".join(f"{k[8:]}{v}" for k, v in s.items()))
+def test_every_pass_schedule_is_bit_exact(ctx, sched, monkeypatch):
+    """The pass planner's knobs (tile size, column width, thread count; read per call) only change the schedule:
+    forward, inverse and the fused coset transform stay bit-exact against the oracle at a multi-pass size."""
+    for k, v in sched.items():
+        monkeypatch.setenv(k, v)
+    logn = 13
+    n = 1 << logn
+    rng = random.Random(900)
+    vecs = [[rng.randrange(R) for _ in range(n)] for _ in range(3)]
+    d = ctx.upload(fe_list_bytes(_mont(vecs[0])))
+    ctx.ntt(d, logn)
+    assert _unmont(bytes_fe_list(ctx.download(d))) == bn.ntt(vecs[0])
+    ctx.ntt(d, logn, inverse=True)
+    assert _unmont(bytes_fe_list(ctx.download(d))) == vecs[0]
+    ds = [ctx.upload(fe_list_bytes(_mont(v))) for v in vecs]
+    ctx.coset_transform(ds, logn)
+    w2n = bn.fr_root(logn + 1)
+    for v, dv in zip(vecs, ds):
+        co = bn.ntt(v, inverse=True)
+        co = [x * pow(w2n, i, R) % R for i, x in enumerate(co)]
+        assert _unmont(bytes_fe_list(ctx.download(dv))) == bn.ntt(co)
