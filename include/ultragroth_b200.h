@@ -87,22 +87,61 @@ int ugb_coset_transform(ugb_ctx* ctx, void* const* d_vecs, int count, int logn);
  * The reference draws r, s (and UltraGroth's r_k) from randombytes_buf (src/groth16.cpp:165-166,
  * src/ultra_groth.cpp:173,345-346) and has no way to pin them; parity tests need one.  r32/s32/rk32 are
  * 32-byte little-endian raw integers (< 2^248 to stay inside the reference's range); NULL r32 or s32
- * returns the prover to random blinding. */
+ * returns the prover to random blinding.
+ * The hook exists for PARITY TESTS only: a proof made with reused blinding scalars is not zero-knowledge. */
 int ugb_prover_set_blinding(void* prover_object, const void* r32, const void* s32, const void* rk32);
 /* the H-MSM scalars (canonical 32-byte integers, domainSize of them) of the last proof */
 int ugb_prover_last_h(void* prover_object, void* h_out, uint64_t bytes);
+/* the RAW MSM results of the last proof, before blinding and assembly (src/groth16.cpp:53-64,153-154; src/ultra_groth.cpp:168):
+ * 448 bytes = A (64) | B1 (64) | B2 (128) | C (64) | H (64) | round C1 (64; zero for Groth16), affine Montgomery, zkey layout */
+int ugb_prover_last_msms(void* prover_object, void* out448);
+/* `count` 32-byte signals of the witness as it stands in HBM after the last proof (UltraGroth: lookup signals filled in) */
+int ugb_prover_last_witness(void* prover_object, void* out, uint64_t first, uint64_t count);
+/* create-time breakdown in ms: base uploads, coefficient CSR build (host threads, overlapped), window tables, total */
+int ugb_prover_create_times(void* prover_object, double* out4);
 /* per-stage CUDA-event times (ms) of the last proof: upload, round, lookup, sort_w, msm_a, msm_b1, msm_b2,
  * msm_c, spmv, intt, ntt, hfinal, sort_h, msm_h, total */
 int ugb_prover_set_timing(void* prover_object, int enable);
 int ugb_prover_last_times(void* prover_object, float* out, int count);
 uint64_t ugb_prover_kernel_launches(void* prover_object);
-/* re-runs the device part of a proof (MSMs + H pipeline) on the witness left in HBM by the previous
- * *_prover_prove call: no host->device input copy (bench.py's device-resident leg) */
+/* One WHOLE proof from the witness (UltraGroth: and lookup arrays) left in HBM by the previous *_prover_prove call: both rounds,
+ * challenge, lookup fill, every MSM, the H pipeline, blinding, assembly, JSON -- everything except the host->device input copy
+ * (bench.py's device-resident leg).  ugb_prover_last_proof reads the proof back (NUL terminated, truncated to the capacities). */
 int ugb_prover_prove_resident(void* prover_object);
+int ugb_prover_last_proof(void* prover_object, char* proof_buffer, uint64_t proof_cap, char* public_buffer, uint64_t public_cap);
 /* per-kernel device time from CUDA events on the launching stream; stats text is "name\tlaunches\tms\n" */
 int ugb_prover_set_profile(void* prover_object, int enable);
 uint64_t ugb_prover_kernel_stats(void* prover_object, char* out, uint64_t cap);
 void* ugb_prover_stream(void* prover_object);
+
+/* ---- the reference's C++ class API behind a C ABI (include/groth16.hpp, include/ultra_groth.hpp wrap these) ----
+ * The zkey sections as HOST pointers, exactly the arguments of Groth16::makeProver<Engine> (src/groth16.hpp:118-136,
+ * src/groth16.cpp:17-45; called from src/prover.cpp:160-189) and UltraGroth::makeProver (src/ultra_groth.hpp:218-247,
+ * src/ultra_groth.cpp:108-159; src/prover.cpp:237-260).  Everything is copied to HBM during the call; the pointers are not kept. */
+typedef struct ugb_zkey_sections {
+    uint32_t nVars, nPublic, domainSize;
+    uint64_t nCoefs;
+    const void *vk_alpha1, *vk_beta1, *vk_beta2, *vk_delta1, *vk_delta2; /* G1 64 B / G2 128 B; UltraGroth: delta = final_delta */
+    const void* coefs;    /* nCoefs packed 44-byte Coef records (zkey section 4 + 4) */
+    const void *pointsA, *pointsB1, *pointsB2, *pointsC /* UltraGroth: final_pointsC */, *pointsH;
+    /* UltraGroth only (ignored for Groth16) */
+    const void* round_delta1;
+    const void* round_pointsC;
+    const uint32_t *round_indexes, *final_round_indexes;
+    uint32_t round_indexes_count, final_round_indexes_count, challenge_index;
+} ugb_zkey_sections;
+int ugb_prover_create_from_sections(void** prover_object, int ultra, const ugb_zkey_sections* sections, char* error_msg,
+                                    unsigned long long error_msg_maxsize);
+/* Groth16::Prover<Engine>::prove(FrElement* wtns) (src/groth16.cpp:48-203): nVars raw 32-byte signals -> proof points A, B, C in the
+ * reference's G1PointAffine / G2PointAffine layout.  Return codes as include/prover.h. */
+int ugb_groth16_prove_raw(void* prover_object, const void* wtns_signals, void* out_A64, void* out_B128, void* out_C64, char* error_msg,
+                          unsigned long long error_msg_maxsize);
+/* UltraGroth::Prover<Engine>::prove(FrElement* wtns, LookupInfo&) (src/ultra_groth.cpp:401-462); wtns_signals is in/out like the
+ * reference's (compute_lookup writes the lookup signals into it, src/ultra_groth.cpp:62-106). */
+int ugb_ultra_groth_prove_raw(void* prover_object, void* wtns_signals, const uint32_t* chunks, uint32_t chunks_len, const uint32_t* frequencies,
+                              uint32_t frequencies_len, const uint32_t* wtns_indxs, const uint32_t* push_indxs, uint32_t wtns_indxs_len,
+                              void* out_A64, void* out_B128, void* out_final_commitment64, void* out_round_commitment64, char* error_msg,
+                              unsigned long long error_msg_maxsize);
 
 /* ---- point-range sharded proving ("MSMs shard by point range across GPUs, partial sums reduced
  * on the host or via NCCL") ----

@@ -15,11 +15,15 @@ def lib():
     global _lib
     if _lib is None:
         path = build_oracle.LIB
-        if not os.path.exists(path):
-            build_oracle.build()
+        build_oracle.build()  # no-op unless the .so is missing or older than cpu_prover.cpp
         L = ctypes.CDLL(path)
         vp, u64, i32 = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int
         L.cpu_prove.argtypes = [vp, u64, vp, u64, vp, vp, vp, i32, vp, vp, vp, vp]
+        L.cpu_prove2.argtypes = [vp, u64, vp, u64, vp, vp, vp, i32, vp, vp, vp, vp, vp]
+        L.cpu_synth_build.argtypes = [i32, i32, u64, i32, ctypes.c_uint32, i32, ctypes.POINTER(vp), ctypes.POINTER(u64), ctypes.POINTER(vp),
+                                      ctypes.POINTER(u64), ctypes.POINTER(vp)]
+        L.cpu_free.argtypes = [vp]
+        L.cpu_free.restype = None
         L.cpu_msm_g1.argtypes = [vp, vp, u64, i32, vp]
         L.cpu_msm_g2.argtypes = [vp, vp, u64, i32, vp]
         L.cpu_ntt.argtypes = [vp, i32, i32, i32]
@@ -42,8 +46,12 @@ def max_threads():
     return int(lib().cpu_max_threads())
 
 
-def prove(zkey, wtns, r, s, rk=0, threads=0, want_h=False, want_witness=False, domain_size=None, n_vars=None):
-    """-> dict(points=bytes(320): A|B|C|R affine Montgomery, h=bytes or None, witness=bytes or None, times_ms=[...])"""
+MSM_SLICES = {"a": (0, 64), "b1": (64, 128), "b2": (128, 256), "c": (256, 320), "h": (320, 384), "round_c": (384, 448)}
+
+
+def prove(zkey, wtns, r, s, rk=0, threads=0, want_h=False, want_witness=False, domain_size=None, n_vars=None, want_msms=False):
+    """-> dict(points=bytes(320): A|B|C|R affine Montgomery, h=bytes or None, witness=bytes or None, times_ms=[...],
+    msms={a,b1,b2,c,h,round_c: affine Montgomery bytes of the RAW MSM results} or None)"""
     zk, wt = _arr(zkey), _arr(wtns)
     enc = lambda x: np.frombuffer(int(x).to_bytes(32, "little"), dtype=np.uint8).copy()
     rr, ss, kk = enc(r), enc(s), enc(rk)
@@ -51,12 +59,34 @@ def prove(zkey, wtns, r, s, rk=0, threads=0, want_h=False, want_witness=False, d
     h = np.zeros(32 * domain_size, dtype=np.uint8) if want_h else None
     w = np.zeros(32 * n_vars, dtype=np.uint8) if want_witness else None
     times = np.zeros(5, dtype=np.float64)
-    rc = lib().cpu_prove(_ptr(zk), zk.nbytes, _ptr(wt), wt.nbytes, _ptr(rr), _ptr(ss), _ptr(kk), threads, _ptr(pts),
-                         _ptr(h) if want_h else None, _ptr(w) if want_witness else None, _ptr(times))
+    mm = np.zeros(448, dtype=np.uint8)
+    rc = lib().cpu_prove2(_ptr(zk), zk.nbytes, _ptr(wt), wt.nbytes, _ptr(rr), _ptr(ss), _ptr(kk), threads, _ptr(pts),
+                          _ptr(h) if want_h else None, _ptr(w) if want_witness else None, _ptr(times), _ptr(mm) if want_msms else None)
     if rc:
         raise RuntimeError(f"cpu_prove failed with code {rc}")
+    mb = mm.tobytes()
     return dict(points=pts.tobytes(), h=h.tobytes() if want_h else None, witness=w.tobytes() if want_witness else None,
-                times_ms=[float(x) for x in times])
+                times_ms=[float(x) for x in times], msms={k: mb[a:b] for k, (a, b) in MSM_SLICES.items()} if want_msms else None)
+
+
+def synth(logn, seed=0xB200, ultra=False, lookup_bits=4, n_chunks=8, threads=0):
+    """CPU generator of the synthetic circuits + valid setup (oracle/cpu_synth.cpp): the same (zkey, wtns, vk json) as the product's
+    ugb_synth_build for the same arguments, without touching the GPU library."""
+    zk, wt, vk = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p()
+    zn, wn = ctypes.c_uint64(), ctypes.c_uint64()
+    rc = lib().cpu_synth_build(1 if ultra else 0, logn, seed, lookup_bits, n_chunks, threads, ctypes.byref(zk), ctypes.byref(zn),
+                               ctypes.byref(wt), ctypes.byref(wn), ctypes.byref(vk))
+    if rc:
+        raise RuntimeError(f"cpu_synth_build failed with code {rc}")
+    try:
+        zkey = np.ctypeslib.as_array(ctypes.cast(zk, ctypes.POINTER(ctypes.c_uint8)), shape=(zn.value,)).copy()
+        wtns = np.ctypeslib.as_array(ctypes.cast(wt, ctypes.POINTER(ctypes.c_uint8)), shape=(wn.value,)).copy()
+        vkj = ctypes.string_at(vk).decode()
+    finally:
+        lib().cpu_free(zk)
+        lib().cpu_free(wt)
+        lib().cpu_free(vk)
+    return zkey, wtns, vkj
 
 
 def msm(group, bases, scalars, n, threads=0):

@@ -112,7 +112,9 @@ def derive_challenge(commitment):
 def compute_lookup(w, chunks, freqs, wtns_idx, push_idx, rand):
     """src/ultra_groth.cpp:62-106; mutates and returns the witness list."""
     inv2 = [pow((i + rand) % R, -1, R) for i in range(len(freqs))]
-    prod = [freqs[i] * inv2[i] % R for i in range(len(freqs))]
+    # RawFr::field.mul(frequencies[i], inv) converts the uint32_t frequency to `int` (build/fr.hpp:251 -> RawFr::set(int),
+    # build/fr.cpp:209-223): a frequency >= 2^31 is read as the NEGATIVE number f - 2^32 and q is added once
+    prod = [(freqs[i] - (1 << 32) if freqs[i] >= (1 << 31) else freqs[i]) * inv2[i] % R for i in range(len(freqs))]
     inv1 = [inv2[ch] for ch in chunks]
     push = [rand] + inv1 + inv2 + prod
     for wi, pi in zip(wtns_idx, push_idx):

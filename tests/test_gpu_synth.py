@@ -23,6 +23,19 @@ def test_fixed_base_mul_vs_oracle(ctx):
         assert g2_from_bytes(out2[128 * i:128 * i + 128]) == (bn.G2.mul_affine(bn.G2_GEN, k) if k else None)
 
 
+@pytest.mark.parametrize("ultra,logn,lookup_bits,chunks", [(False, 4, 0, 0), (False, 12, 0, 0), (True, 7, 3, 20), (True, 13, 7, 2048)])
+def test_gpu_and_cpu_generators_emit_the_same_files(ctx, ultra, logn, lookup_bits, chunks):
+    """The GPU generator (ugb_synth_build, the fixed-base multiplications on the device) and the oracle's CPU generator
+    (oracle/cpu_synth.cpp, used by bench.py's CPU arm so that it never loads the product library) must produce identical bytes:
+    zkey, witness and verification key."""
+    from oracle import cpu_prover as cp
+    gz, gw, gv = ctx.synth(logn, seed=4242 + logn, ultra=ultra, lookup_bits=lookup_bits, n_chunks=chunks)
+    cz, cw, cv = cp.synth(logn, seed=4242 + logn, ultra=ultra, lookup_bits=lookup_bits, n_chunks=chunks)
+    assert gz.tobytes() == cz.tobytes()
+    assert gw.tobytes() == cw.tobytes()
+    assert gv == cv
+
+
 @pytest.mark.parametrize("logn", [2, 5, 8])
 def test_synth_groth16_small_bit_exact(ctx, logn):
     zk, wt, vkj = ctx.synth(logn, seed=100 + logn)

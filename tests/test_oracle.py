@@ -189,6 +189,73 @@ def test_cpp_oracle_matches_python_oracle_on_testdata(testdata):
     assert [int.from_bytes(res["h"][i:i + 32], "little") for i in range(0, 32 * 1024, 32)] == inter["h"]
 
 
+def _check_msms(msms, inter, ultra):
+    assert g1_from_bytes(msms["a"]) == inter["msm_a"]
+    assert g1_from_bytes(msms["b1"]) == inter["msm_b1"]
+    assert g2_from_bytes(msms["b2"]) == inter["msm_b2"]
+    assert g1_from_bytes(msms["c"]) == inter["msm_c"]
+    assert g1_from_bytes(msms["h"]) == inter["msm_h"]
+    if ultra:
+        assert g1_from_bytes(msms["round_c"]) == inter["msm_round"]
+
+
+def test_cpp_oracle_raw_msm_results_on_testdata(testdata):
+    """The per-MSM taps the full-size GPU parity tests compare against (cpu_prove2's out_msms) equal the big-int oracle's."""
+    zk, wt, vk = testdata
+    r, s = 99991, (1 << 200) + 3
+    _, _, inter = og.groth16_prove(zk, wt, r, s, want_intermediates=True)
+    res = cp.prove(zk, wt, r, s, threads=2, want_msms=True)
+    _check_msms(res["msms"], inter, False)
+
+
+@pytest.mark.parametrize("ultra,logn", [(False, 6), (True, 7), (True, 9)])
+def test_cpu_synth_setup_is_valid_and_cpp_oracle_matches_python(ultra, logn):
+    """oracle/cpu_synth.cpp (the CPU twin of the product's synthetic-setup generator): the key is a VALID setup -- the oracle's
+    proof verifies under the reference's verifier equation (src/groth16.cpp:298-364, src/ultra_groth.cpp:581-648) and a tampered
+    public input fails -- and on it the C++ oracle equals the Python big-int oracle: raw MSMs, H scalars, the witness after
+    compute_lookup (src/ultra_groth.cpp:62-106), proof points."""
+    zk, wt, vkj = cp.synth(logn, seed=900 + logn, ultra=ultra, lookup_bits=3, n_chunks=40, threads=2)
+    zk, wt = zk.tobytes(), wt.tobytes()
+    rk, r, s = (1 << 199) + 7, 424242, (1 << 247) + 1
+    n_vars = int.from_bytes(wt[60:64], "little")
+    if ultra:
+        proof, public, inter = og.ultragroth_prove(zk, wt, rk, r, s, want_intermediates=True)
+        assert og.ultragroth_verify(og.vk_from_ultragroth_json(vkj), proof, public)
+        assert not og.ultragroth_verify(og.vk_from_ultragroth_json(vkj), proof, [(public[0] + 1) % bn.R])
+    else:
+        proof, public, inter = og.groth16_prove(zk, wt, r, s, want_intermediates=True)
+        assert og.groth16_verify(og.vk_from_snarkjs_json(vkj), proof, public)
+        assert not og.groth16_verify(og.vk_from_snarkjs_json(vkj), proof, [(public[0] + 1) % bn.R])
+    res = cp.prove(zk, wt, r, s, rk, threads=2, want_h=True, want_witness=True, domain_size=1 << logn, n_vars=n_vars, want_msms=True)
+    _check_msms(res["msms"], inter, ultra)
+    assert [int.from_bytes(res["h"][i:i + 32], "little") for i in range(0, 32 << logn, 32)] == inter["h"]
+    p = res["points"]
+    assert g1_from_bytes(p[0:64]) == proof["pi_a"] and g2_from_bytes(p[64:192]) == proof["pi_b"]
+    assert g1_from_bytes(p[192:256]) == proof["pi_f" if ultra else "pi_c"]
+    if ultra:
+        assert g1_from_bytes(p[256:320]) == proof["pi_r"]
+        assert [int.from_bytes(res["witness"][i:i + 32], "little") for i in range(0, 32 * n_vars, 32)] == [x % bn.R for x in inter["witness"]]
+
+
+def test_lookup_frequency_int_conversion_in_both_oracles():
+    """RawFr::field.mul(frequencies[i], inv) converts the uint32_t frequency to `int` (build/fr.hpp:251 -> RawFr::set(int),
+    build/fr.cpp:209-223): a frequency >= 2^31 is a negative number.  Both oracles restate that."""
+    from oracle import formats as fm
+    zk, wt, _ = cp.synth(7, seed=33, ultra=True, lookup_bits=3, n_chunks=20, threads=2)
+    zk, wt = zk.tobytes(), bytearray(wt.tobytes())
+    off4 = fm.BinFile(bytes(wt), "wtns", 2).sections[4][0][0]
+    wt[off4 + 4:off4 + 8] = (0xfffffffe).to_bytes(4, "little")  # frequency[1] = -2
+    wt = bytes(wt)
+    n_vars = int.from_bytes(wt[60:64], "little")
+    _, _, inter = og.ultragroth_prove(zk, wt, 5, 6, 7, want_intermediates=True)
+    res = cp.prove(zk, wt, 6, 7, 5, threads=2, want_witness=True, n_vars=n_vars)
+    got = [int.from_bytes(res["witness"][i:i + 32], "little") for i in range(0, 32 * n_vars, 32)]
+    assert got == [x % bn.R for x in inter["witness"]]
+    # prod_1 = -2 / (1 + rand): the last T signals are the prod values (synthetic layout), T = 8
+    rand = inter["rand"] % bn.R
+    assert got[n_vars - 8 + 1] == (bn.R - 2) * pow((1 + rand) % bn.R, -1, bn.R) % bn.R
+
+
 @pytest.mark.parametrize("group", [1, 2])
 def test_cpp_msm_vs_python(group):
     C, gen = (bn.G1, bn.G1_GEN) if group == 1 else (bn.G2, bn.G2_GEN)

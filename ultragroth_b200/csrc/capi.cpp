@@ -27,6 +27,7 @@ struct ugb_ctx {
 };
 
 static thread_local std::string g_last_error;
+namespace ug { void set_last_error(const std::string& msg) { g_last_error = msg; } }
 
 #define UGB_TRY try {
 #define UGB_CATCH                                                     \

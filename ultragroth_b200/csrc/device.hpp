@@ -92,6 +92,9 @@ public:
         }
         return b.ptr;
     }
+    // once-per-context markers (e.g. per-device function attributes already set)
+    bool flag(const std::string& name) const { return flags_.count(name) != 0; }
+    void set_flag(const std::string& name) { flags_[name] = true; }
     void sync() { activate(); UG_CUDA_CHECK(cudaStreamSynchronize(stream)); }
     // kernel profiling: prof_begin / prof_end bracket one launch; prof_collect folds finished pairs into kernel_stats
     void prof_begin(const char* name) {
@@ -149,6 +152,7 @@ private:
     std::map<std::string, DeviceBuffer> ws_;
     std::map<std::string, DeviceBuffer> pinned_;
     std::map<std::string, cudaEvent_t> events_;
+    std::map<std::string, bool> flags_;
 };
 
 #define UG_LAUNCH_CHECK(ctx)                \

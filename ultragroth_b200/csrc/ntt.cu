@@ -156,11 +156,11 @@ void ntt_run(DeviceCtx& ctx, NttTables& tabs, Fr* const* d_vecs, int count, int 
     if (count < 1 || count > 3) throw std::runtime_error("ultragroth_b200: ntt_run takes 1..3 vectors");
     if (logn < 0 || logn > 27) throw std::runtime_error("ultragroth_b200: NTT size out of range");
     ctx.activate();
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in for > 48 KiB of dynamic shared memory is a per-DEVICE function attribute: remembered per context, not per process
+    if (!ctx.flag("ntt.smem_optin")) {
         UG_CUDA_CHECK(cudaFuncSetAttribute(k_ntt_pass<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         UG_CUDA_CHECK(cudaFuncSetAttribute(k_ntt_pass<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
+        ctx.set_flag("ntt.smem_optin");
     }
     std::vector<PassShape> sched;
     if (logn == 0) sched.push_back({0, 0, 0});

@@ -12,6 +12,7 @@
 #include <cstring>
 #include <fstream>
 #include <memory>
+#include <mutex>
 #include <random>
 #include <string>
 
@@ -19,6 +20,8 @@
 #include "prover_dev.hpp"
 
 using namespace ug;
+
+namespace ug { void set_last_error(const std::string& msg); }
 
 namespace {
 
@@ -179,30 +182,66 @@ int pick_device() {
 
 class ProverBase {
 public:
+    // from a zkey file image (src/prover.cpp:144-216, 219-309)
     ProverBase(const void* zkey_buffer, unsigned long long zkey_size, bool ultra, uint32_t shard_rank = 0, uint32_t shard_world = 1,
-               bool tables = true)
-        : zkey(zkey_buffer, zkey_size, "zkey", 1), hdr(load_zkey_header(zkey, ultra)) {
+               bool tables = true) {
+        BinFile zkey(zkey_buffer, zkey_size, "zkey", 1);
+        hdr = load_zkey_header(zkey, ultra);
         if (!prime_is_bn254_r(hdr.rPrime, hdr.n8r)) throw std::invalid_argument("zkey curve not supported");
         // the header points (alpha, beta, delta...) are copied: the zkey buffer is only borrowed during create
         // for everything that goes to HBM, and the reference's file-path variant frees it right after create
         hdr_copy.assign(zkey.data(2), zkey.data(2) + zkey.size(2));
-        BinFile::Section s{hdr_copy.data(), hdr_copy.size()};
-        rebase(s);
-        dev.reset(new ProverDevice(pick_device(), zkey, hdr, shard_rank, shard_world, tables));
+        rebase(zkey.data(2), hdr_copy.data());
+        dev.reset(new ProverDevice(pick_device(), zkey_data_from_file(zkey, hdr), shard_rank, shard_world, tables));
+    }
+    // from the section pointers of the reference's C++ class API (ugb_prover_create_from_sections)
+    ProverBase(const ugb_zkey_sections& z, bool ultra, bool tables = true) {
+        hdr.ultra = ultra;
+        hdr.n8q = hdr.n8r = 32;
+        hdr.nVars = z.nVars; hdr.nPublic = z.nPublic; hdr.domainSize = z.domainSize; hdr.nCoefs = z.nCoefs;
+        hdr.num_indexes_c1 = z.round_indexes_count; hdr.num_indexes_c2 = z.final_round_indexes_count; hdr.rand_indx = z.challenge_index;
+        // header points copied into one private block: alpha1 | beta1 | beta2 | delta1 | delta2 | round_delta1
+        if (!z.vk_alpha1 || !z.vk_beta1 || !z.vk_beta2 || !z.vk_delta1 || !z.vk_delta2 || (ultra && !z.round_delta1))
+            throw std::invalid_argument("Null verification-key point");
+        hdr_copy.resize(64 + 64 + 128 + 64 + 128 + 64, 0);
+        uint8_t* p = hdr_copy.data();
+        memcpy(p, z.vk_alpha1, 64); hdr.alpha1 = p; p += 64;
+        memcpy(p, z.vk_beta1, 64); hdr.beta1 = p; p += 64;
+        memcpy(p, z.vk_beta2, 128); hdr.beta2 = p; p += 128;
+        memcpy(p, z.vk_delta1, 64); hdr.final_delta1 = p; p += 64;
+        memcpy(p, z.vk_delta2, 128); hdr.final_delta2 = p; p += 128;
+        if (ultra) { memcpy(p, z.round_delta1, 64); hdr.round_delta1 = p; }
+        ZkeyData d;
+        d.ultra = ultra;
+        d.nVars = z.nVars; d.nPublic = z.nPublic; d.domainSize = z.domainSize; d.nCoefs = z.nCoefs;
+        d.coefs = (const uint8_t*)z.coefs;
+        d.A = (const uint8_t*)z.pointsA; d.B1 = (const uint8_t*)z.pointsB1; d.B2 = (const uint8_t*)z.pointsB2;
+        d.C = (const uint8_t*)z.pointsC; d.H = (const uint8_t*)z.pointsH; d.C1 = (const uint8_t*)z.round_pointsC;
+        d.idx_c1 = (const uint8_t*)z.round_indexes; d.idx_c2 = (const uint8_t*)z.final_round_indexes;
+        d.n_c1 = z.round_indexes_count; d.n_c2 = z.final_round_indexes_count;
+        if (!d.coefs && d.nCoefs) throw std::invalid_argument("Null coefficient pointer");
+        if (!d.A || !d.B1 || !d.B2 || !d.C || !d.H || (ultra && (!d.C1 || (!d.idx_c1 && d.n_c1) || (!d.idx_c2 && d.n_c2))))
+            throw std::invalid_argument("Null zkey section pointer");
+        dev.reset(new ProverDevice(pick_device(), d, 0, 1, tables));
     }
     virtual ~ProverBase() {}
 
-    BinFile zkey;  // only valid during construction (borrowed buffer)
     ZkeyHeader hdr;
     std::vector<uint8_t> hdr_copy;
     std::unique_ptr<ProverDevice> dev;
     Blinding blinding;
+    // One prover object serialises its callers: all mutable proof state (witness, a/b/c, workspaces, pinned partial-sum slots, the
+    // stream) lives in `dev`.  The reference allocates per call and so tolerates concurrent prove() calls; this keeps that safe.
+    std::mutex mu;
+    // parity taps of the last proof (ugb_prover_last_msms / _last_proof): the raw MSM results before blinding and assembly
+    ProofMsms last_msms;
+    bool has_last = false;
+    std::string last_proof, last_public;
     bool is_ultra() const { return hdr.ultra; }
 
 protected:
-    void rebase(const BinFile::Section& s) {
-        const uint8_t* old = zkey.data(2);
-        auto mv = [&](const uint8_t*& p) { if (p) p = s.start + (p - old); };
+    void rebase(const uint8_t* old, const uint8_t* now) {
+        auto mv = [&](const uint8_t*& p) { if (p) p = now + (p - old); };
         mv(hdr.qPrime); mv(hdr.rPrime); mv(hdr.alpha1); mv(hdr.beta1); mv(hdr.beta2); mv(hdr.gamma2);
         mv(hdr.round_delta1); mv(hdr.round_delta2); mv(hdr.final_delta1); mv(hdr.final_delta2);
     }
@@ -223,6 +262,7 @@ class Groth16Prover : public ProverBase {
 public:
     Groth16Prover(const void* zkey_buffer, unsigned long long zkey_size, uint32_t shard_rank = 0, uint32_t shard_world = 1, bool tables = true)
         : ProverBase(zkey_buffer, zkey_size, false, shard_rank, shard_world, tables) {}
+    explicit Groth16Prover(const ugb_zkey_sections& z) : ProverBase(z, false) {}
 
     const uint8_t* check_witness(const void* wtns_buffer, unsigned long long wtns_size) {
         BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
@@ -238,21 +278,41 @@ public:
     void msms(const void* wtns_buffer, unsigned long long wtns_size, ProofMsms& m) {
         dev->prove_groth16(check_witness(wtns_buffer, wtns_size), m);
     }
-    // host half: blinding, assembly, JSON (src/groth16.cpp:158-250)
-    void finish(const ProofMsms& m, const uint8_t* w, std::string& stringProof, std::string& stringPublic) {
+    // host half: blinding and assembly (src/groth16.cpp:158-203)
+    void finish_points(const ProofMsms& m, HG1Affine& A, HG2Affine& B, HG1Affine& C) {
         Scalar r = blinding.fixed ? blinding.r : random_blinding();
         Scalar s = blinding.fixed ? blinding.s : random_blinding();
+        assemble(hdr, m, r, s, nullptr, A, B, C);
+        last_msms = m;
+        has_last = true;
+    }
+    // ... and JSON (src/groth16.cpp:205-250, src/prover.cpp:89-117)
+    void finish(const ProofMsms& m, const uint8_t* w, std::string& stringProof, std::string& stringPublic) {
         HG1Affine A, C;
         HG2Affine B;
-        assemble(hdr, m, r, s, nullptr, A, B, C);
+        finish_points(m, A, B, C);
         stringProof = "{\"pi_a\":" + g1_json(A) + ",\"pi_b\":" + g2_json(B) + ",\"pi_c\":" + g1_json(C) + ",\"protocol\":\"groth16\"}";
         stringPublic = public_json(w + 32, hdr.nPublic, 0);
+    }
+    // Groth16::Prover<Engine>::prove(FrElement* wtns) (src/groth16.cpp:48-203): nVars raw 32-byte signals in, proof points out
+    void prove_raw(const uint8_t* w, HG1Affine& A, HG2Affine& B, HG1Affine& C) {
+        ProofMsms m;
+        dev->prove_groth16(w, m);
+        finish_points(m, A, B, C);
     }
     void prove(const void* wtns_buffer, unsigned long long wtns_size, std::string& stringProof, std::string& stringPublic) {
         const uint8_t* w = check_witness(wtns_buffer, wtns_size);
         ProofMsms m;
         dev->prove_groth16(w, m);
         finish(m, w, stringProof, stringPublic);
+    }
+    // a whole proof from the witness already resident in HBM (bench.py's device-resident leg): same device work and host tail
+    void prove_resident(std::string& stringProof, std::string& stringPublic) {
+        ProofMsms m;
+        dev->prove_resident(m);
+        std::vector<uint8_t> pub((size_t)(hdr.nPublic + 1) * 32);
+        dev->download_witness(pub.data(), 0, hdr.nPublic + 1);
+        finish(m, pub.data(), stringProof, stringPublic);
     }
     unsigned long long proofBufferMinSize() const { return ProofBufferMinSize(); }
     unsigned long long publicBufferMinSize() const { return PublicBufferMinSize(hdr.nPublic); }
@@ -262,8 +322,11 @@ class UltraGrothProver : public ProverBase {
 public:
     UltraGrothProver(const void* zkey_buffer, unsigned long long zkey_size, uint32_t shard_rank = 0, uint32_t shard_world = 1, bool tables = true)
         : ProverBase(zkey_buffer, zkey_size, true, shard_rank, shard_world, tables) {}
+    explicit UltraGrothProver(const ugb_zkey_sections& z) : ProverBase(z, true) {}
 
-    struct Lookup { std::vector<uint32_t> chunks, freqs, widx, pidx; };
+    // LookupInfo (src/prover.cpp:287-292, src/ultra_groth.hpp:22-61): four u32 arrays, BORROWED from the caller's wtns buffer
+    // (any alignment); they are copied to HBM as they are and range-checked there (k_lookup_push)
+    struct Lookup { const void *chunks = nullptr, *freqs = nullptr, *widx = nullptr, *pidx = nullptr; uint32_t chunks_len = 0, freqs_len = 0, idx_len = 0; };
 
     const uint8_t* check_witness(const BinFile& wtns) {
         WtnsHeader wh = load_wtns_header(wtns);
@@ -274,24 +337,22 @@ public:
         if (wtns.size(2) < (uint64_t)hdr.nVars * 32) throw std::range_error("wtns section too short: signals");
         return wtns.data(2);
     }
-    // LookupInfo (src/prover.cpp:287-292, src/ultra_groth.hpp:22-61): four u32 arrays
     void load_lookup(const BinFile& wtns, Lookup& lk) {
-        auto u32s = [&](uint32_t id, std::vector<uint32_t>& v) {
-            uint64_t cnt = wtns.size(id) >> 2;
-            v.resize(cnt);
-            if (cnt) memcpy(v.data(), wtns.data(id), cnt * 4);
-        };
-        u32s(3, lk.chunks); u32s(4, lk.freqs); u32s(5, lk.widx); u32s(6, lk.pidx);
-        if (lk.widx.size() != lk.pidx.size()) {
-            // the reference iterates wtns_indxs_len entries of both arrays
-            if (lk.pidx.size() < lk.widx.size()) throw std::range_error("wtns push index section shorter than witness index section");
-        }
+        lk.chunks = wtns.data(3); lk.freqs = wtns.data(4); lk.widx = wtns.data(5); lk.pidx = wtns.data(6);
+        if ((wtns.size(3) >> 2) > 0xffffffffull || (wtns.size(4) >> 2) > 0xffffffffull || (wtns.size(5) >> 2) > 0xffffffffull)
+            throw std::range_error("wtns lookup section too long");
+        lk.chunks_len = (uint32_t)(wtns.size(3) >> 2);
+        lk.freqs_len = (uint32_t)(wtns.size(4) >> 2);
+        lk.idx_len = (uint32_t)(wtns.size(5) >> 2);
+        // the reference iterates wtns_indxs_len entries of both arrays
+        if ((wtns.size(6) >> 2) < lk.idx_len) throw std::range_error("wtns push index section shorter than witness index section");
     }
     const uint8_t* check_witness(const BinFile& wtns, Lookup& lk) {
         const uint8_t* w = check_witness(wtns);
         load_lookup(wtns, lk);
         return w;
     }
+    void stage(const Lookup& lk) { dev->ultra_lookup_stage(lk.chunks, lk.chunks_len, lk.freqs, lk.freqs_len, lk.widx, lk.pidx, lk.idx_len); }
     // round 1, device half: upload + MSM(round_pointsC, round_wtns) over this prover's point range
     void round_msm(const uint8_t* w, HG1XYZZ& partial) {
         dev->ultra_upload_witness(w);
@@ -299,44 +360,73 @@ public:
     }
     // commitment = (sum of the round MSM) + r_k * final_delta1 (src/ultra_groth.cpp:161-184), then the challenge,
     // the lookup fill and the final-round MSMs over this prover's point range
-    void final_msms(HG1XYZZ commit, const Scalar& rk, const Lookup& lk, HG1Affine& commit_aff, ProofMsms& m, bool staged = false) {
+    void final_msms(HG1XYZZ commit, const Scalar& rk, const Lookup* lk, HG1Affine& commit_aff, ProofMsms& m) {
+        m.round_c = commit;  // the raw round MSM (parity tap)
         HG1XYZZ fdelta1 = from_affine_bytes<HFq>(hdr.final_delta1);
         pt_add(commit, pt_mul(fdelta1, rk));
         commit_aff = pt_to_affine(commit);
         HFr rand_mont = derive_challenge(commit_aff);  // src/ultra_groth.cpp:32-58
-        if (!staged)
-            dev->ultra_lookup_stage(lk.chunks.data(), (uint32_t)lk.chunks.size(), lk.freqs.data(), (uint32_t)lk.freqs.size(), lk.widx.data(),
-                                    lk.pidx.data(), (uint32_t)lk.widx.size());
+        if (lk) stage(*lk);
         dev->ultra_lookup_apply(rand_mont);
+        HG1XYZZ raw_round = m.round_c;
         dev->ultra_final_msms(m);
+        m.round_c = raw_round;
     }
-    void finish(const ProofMsms& m, const Scalar& rk, const HG1Affine& commit_aff, std::string& stringProof, std::string& stringPublic) {
+    void finish_points(const ProofMsms& m, const Scalar& rk, HG1Affine& A, HG2Affine& B, HG1Affine& C) {
         Scalar r = blinding.fixed ? blinding.r : random_blinding();
         Scalar s = blinding.fixed ? blinding.s : random_blinding();
+        assemble(hdr, m, r, s, &rk, A, B, C);
+        last_msms = m;
+        has_last = true;
+    }
+    void finish(const ProofMsms& m, const Scalar& rk, const HG1Affine& commit_aff, std::string& stringProof, std::string& stringPublic) {
         HG1Affine A, C;
         HG2Affine B;
-        assemble(hdr, m, r, s, &rk, A, B, C);
+        finish_points(m, rk, A, B, C);
         stringProof = "{\"pi_a\":" + g1_json(A) + ",\"pi_b\":" + g2_json(B) + ",\"pi_f\":" + g1_json(C) + ",\"pi_r\":" + g1_json(commit_aff) +
                       ",\"protocol\":\"ultragroth\"}";
         std::vector<uint8_t> pub((size_t)hdr.nPublic * 32);
         if (hdr.nPublic) dev->download_witness(pub.data(), 1, hdr.nPublic);
         stringPublic = public_json(pub.data(), hdr.nPublic, hdr.rand_indx);
     }
+    // UltraGroth::Prover::prove(FrElement* wtns, LookupInfo&) (src/ultra_groth.cpp:401-462): raw signals + lookup arrays in, points out.
+    // wtns_out: the reference fills the lookup signals into the CALLER's witness (compute_lookup writes `signals`); when non-null the
+    // same nVars*32 bytes are written back.
+    void prove_raw(const uint8_t* w, const Lookup& lk, HG1Affine& A, HG2Affine& B, HG1Affine& C, HG1Affine& R, uint8_t* wtns_out) {
+        // the witness copy is asynchronous; the lookup arrays follow it on the same stream
+        dev->ultra_upload_witness(w);
+        stage(lk);
+        HG1XYZZ commit;
+        dev->ultra_round_msm(commit);
+        Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
+        ProofMsms m;
+        final_msms(commit, rk, nullptr, R, m);
+        finish_points(m, rk, A, B, C);
+        if (wtns_out) dev->download_witness(wtns_out, 0, hdr.nVars);
+    }
     void prove(const void* wtns_buffer, unsigned long long wtns_size, std::string& stringProof, std::string& stringPublic) {
         BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
         const uint8_t* w = check_witness(wtns);
-        // the witness copy is asynchronous: the lookup arrays are unpacked, range-checked and staged while it is in flight
         dev->ultra_upload_witness(w);
         Lookup lk;
         load_lookup(wtns, lk);
-        dev->ultra_lookup_stage(lk.chunks.data(), (uint32_t)lk.chunks.size(), lk.freqs.data(), (uint32_t)lk.freqs.size(), lk.widx.data(),
-                                lk.pidx.data(), (uint32_t)lk.widx.size());
+        stage(lk);
         HG1XYZZ commit;
         dev->ultra_round_msm(commit);
         Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
         HG1Affine commit_aff;
         ProofMsms m;
-        final_msms(commit, rk, lk, commit_aff, m, true);
+        final_msms(commit, rk, nullptr, commit_aff, m);
+        finish(m, rk, commit_aff, stringProof, stringPublic);
+    }
+    // a whole proof (both rounds, challenge, lookup fill, assembly) from the witness and lookup arrays left in HBM by the previous proof
+    void prove_resident(std::string& stringProof, std::string& stringPublic) {
+        HG1XYZZ commit;
+        dev->ultra_round_msm(commit);
+        Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
+        HG1Affine commit_aff;
+        ProofMsms m;
+        final_msms(commit, rk, nullptr, commit_aff, m);
         finish(m, rk, commit_aff, stringProof, stringPublic);
     }
     unsigned long long proofBufferMinSize() const { return ProofBufferMinSizeUltraGroth(); }
@@ -395,6 +485,7 @@ int prover_prove_impl(void* prover_object, const void* wtns_buffer, unsigned lon
     if (public_buffer == NULL) throw std::invalid_argument("Null public buffer");
     if (public_size == NULL) throw std::invalid_argument("Null public size");
     P* prover = static_cast<P*>(static_cast<ProverBase*>(prover_object));
+    std::lock_guard<std::mutex> guard(prover->mu);
     CheckAndUpdateBufferSizes(prover->proofBufferMinSize(), proof_size, prover->publicBufferMinSize(), public_size, "Minimum");
     std::string stringProof, stringPublic;
     prover->prove(wtns_buffer, wtns_size, stringProof, stringPublic);
@@ -551,6 +642,7 @@ int ultra_groth_prover_zkey_file(const char* zkey_file_path, const void* wtns_bu
 int ugb_prover_set_blinding(void* prover_object, const void* r32, const void* s32, const void* rk32) {
     if (!prover_object) return UGB_ERROR;
     ProverBase* p = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(p->mu);
     if (!r32 || !s32) { p->blinding.fixed = false; return UGB_OK; }
     p->blinding.fixed = true;
     memcpy(&p->blinding.r, r32, 32);
@@ -558,15 +650,51 @@ int ugb_prover_set_blinding(void* prover_object, const void* r32, const void* s3
     if (rk32) memcpy(&p->blinding.rk, rk32, 32); else memset(&p->blinding.rk, 0, 32);
     return UGB_OK;
 }
-int ugb_prover_last_h(void* prover_object, void* h_out, uint64_t bytes) {
-    if (!prover_object) return UGB_ERROR;
-    try {
-        ProverBase* p = static_cast<ProverBase*>(prover_object);
-        std::vector<uint8_t> h;
-        p->dev->download_h(h);
-        memcpy(h_out, h.data(), std::min<uint64_t>(bytes, h.size()));
-    } catch (...) { return UGB_ERROR; }
+#define EXT_TRY try {
+#define EXT_CATCH                                                                 \
+    }                                                                             \
+    catch (const std::exception& e) { ug::set_last_error(e.what()); return UGB_ERROR; } \
+    catch (...) { ug::set_last_error("unknown error"); return UGB_ERROR; }        \
     return UGB_OK;
+
+int ugb_prover_last_h(void* prover_object, void* h_out, uint64_t bytes) {
+    EXT_TRY
+    if (!prover_object || !h_out) throw std::invalid_argument("Null argument");
+    ProverBase* p = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(p->mu);
+    std::vector<uint8_t> h;
+    p->dev->download_h(h);
+    memcpy(h_out, h.data(), std::min<uint64_t>(bytes, h.size()));
+    EXT_CATCH
+}
+// 448 bytes: A (64) | B1 (64) | B2 (128) | C (64) | H (64) | round C1 (64, zero for Groth16), affine Montgomery, zkey layout
+int ugb_prover_last_msms(void* prover_object, void* out448) {
+    EXT_TRY
+    if (!prover_object || !out448) throw std::invalid_argument("Null argument");
+    ProverBase* p = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(p->mu);
+    if (!p->has_last) throw std::runtime_error("no proof has been made with this prover yet");
+    const ProofMsms& m = p->last_msms;
+    uint8_t* o = (uint8_t*)out448;
+    HG1Affine t;
+    HG2Affine t2 = pt_to_affine(m.b2);
+    t = pt_to_affine(m.a); memcpy(o, &t, 64);
+    t = pt_to_affine(m.b1); memcpy(o + 64, &t, 64);
+    memcpy(o + 128, &t2, 128);
+    t = pt_to_affine(m.c); memcpy(o + 256, &t, 64);
+    t = pt_to_affine(m.h); memcpy(o + 320, &t, 64);
+    if (p->is_ultra()) { t = pt_to_affine(m.round_c); memcpy(o + 384, &t, 64); }
+    else memset(o + 384, 0, 64);
+    EXT_CATCH
+}
+int ugb_prover_last_witness(void* prover_object, void* out, uint64_t first, uint64_t count) {
+    EXT_TRY
+    if (!prover_object || !out) throw std::invalid_argument("Null argument");
+    ProverBase* p = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(p->mu);
+    if (first + count > p->hdr.nVars) throw std::range_error("witness range out of bounds");
+    p->dev->download_witness((uint8_t*)out, first, count);
+    EXT_CATCH
 }
 int ugb_prover_set_timing(void* prover_object, int enable) {
     if (!prover_object) return UGB_ERROR;
@@ -580,13 +708,33 @@ int ugb_prover_last_times(void* prover_object, float* out, int count) {
     for (int i = 0; i < count && i < (int)(sizeof(v) / sizeof(v[0])); i++) out[i] = v[i];
     return UGB_OK;
 }
-int ugb_prover_prove_resident(void* prover_object) {
-    if (!prover_object) return UGB_ERROR;
-    try {
-        ProofMsms m;
-        static_cast<ProverBase*>(prover_object)->dev->prove_resident(m);
-    } catch (...) { return UGB_ERROR; }
+int ugb_prover_create_times(void* prover_object, double* out4) {
+    if (!prover_object || !out4) return UGB_ERROR;
+    for (int i = 0; i < 4; i++) out4[i] = static_cast<ProverBase*>(prover_object)->dev->create_ms[i];
     return UGB_OK;
+}
+// One WHOLE proof from the witness (and, UltraGroth, lookup arrays) left in HBM by the previous *_prover_prove call: both rounds,
+// challenge, lookup fill, every MSM, the H pipeline, blinding, assembly and JSON -- everything except the host->device input copy.
+// The proof is kept and can be read back with ugb_prover_last_proof.
+int ugb_prover_prove_resident(void* prover_object) {
+    EXT_TRY
+    if (!prover_object) throw std::invalid_argument("Null prover object");
+    ProverBase* p = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(p->mu);
+    if (!p->has_last) throw std::runtime_error("ugb_prover_prove_resident needs a previous *_prover_prove call (no witness in HBM yet)");
+    if (p->is_ultra()) static_cast<UltraGrothProver*>(p)->prove_resident(p->last_proof, p->last_public);
+    else static_cast<Groth16Prover*>(p)->prove_resident(p->last_proof, p->last_public);
+    EXT_CATCH
+}
+// proof / public JSON of the last ugb_prover_prove_resident call (NUL terminated, truncated to the capacities)
+int ugb_prover_last_proof(void* prover_object, char* proof_buffer, uint64_t proof_cap, char* public_buffer, uint64_t public_cap) {
+    EXT_TRY
+    if (!prover_object) throw std::invalid_argument("Null prover object");
+    ProverBase* p = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(p->mu);
+    if (proof_buffer && proof_cap) { strncpy(proof_buffer, p->last_proof.c_str(), proof_cap - 1); proof_buffer[proof_cap - 1] = 0; }
+    if (public_buffer && public_cap) { strncpy(public_buffer, p->last_public.c_str(), public_cap - 1); public_buffer[public_cap - 1] = 0; }
+    EXT_CATCH
 }
 int ugb_prover_set_profile(void* prover_object, int enable) {
     if (!prover_object) return UGB_ERROR;
@@ -615,6 +763,57 @@ void* ugb_prover_stream(void* prover_object) {
 }
 
 
+// ---- the reference's C++ class API, C-ABI side (include/groth16.hpp / include/ultra_groth.hpp wrap these) ----
+// Groth16::makeProver<Engine>(nVars, nPublic, domainSize, nCoefs, vk pointers, coefs, pointsA..H) (src/groth16.cpp:17-45) and
+// UltraGroth::makeProver (src/ultra_groth.cpp:108-159): the zkey sections as HOST pointers; everything is copied to HBM here.
+int ugb_prover_create_from_sections(void** prover_object, int ultra, const ugb_zkey_sections* sections, char* error_msg,
+                                    unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (prover_object == NULL) throw std::invalid_argument("Null prover object");
+    if (sections == NULL) throw std::invalid_argument("Null zkey sections");
+    if (ultra) *prover_object = static_cast<ProverBase*>(new UltraGrothProver(*sections));
+    else *prover_object = static_cast<ProverBase*>(new Groth16Prover(*sections));
+    API_CATCH_CREATE
+}
+
+// Groth16::Prover<Engine>::prove(FrElement* wtns) (src/groth16.cpp:48-203): nVars raw (non-Montgomery) 32-byte signals in; the proof
+// points out in the reference's G1PointAffine / G2PointAffine layout (Montgomery coordinates, zkey layout).
+int ugb_groth16_prove_raw(void* prover_object, const void* wtns_signals, void* out_A64, void* out_B128, void* out_C64, char* error_msg,
+                          unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !wtns_signals || !out_A64 || !out_B128 || !out_C64) throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    if (b->is_ultra()) throw std::invalid_argument("not a groth16 prover");
+    HG1Affine A, C;
+    HG2Affine B;
+    static_cast<Groth16Prover*>(b)->prove_raw((const uint8_t*)wtns_signals, A, B, C);
+    memcpy(out_A64, &A, 64); memcpy(out_B128, &B, 128); memcpy(out_C64, &C, 64);
+    API_CATCH_PROVE
+}
+
+// UltraGroth::Prover<Engine>::prove(FrElement* wtns, LookupInfo&) (src/ultra_groth.cpp:401-462).  wtns_signals is IN/OUT like the
+// reference's: compute_lookup's signals (src/ultra_groth.cpp:62-106) are written back into it.
+int ugb_ultra_groth_prove_raw(void* prover_object, void* wtns_signals, const uint32_t* chunks, uint32_t chunks_len, const uint32_t* frequencies,
+                              uint32_t frequencies_len, const uint32_t* wtns_indxs, const uint32_t* push_indxs, uint32_t wtns_indxs_len,
+                              void* out_A64, void* out_B128, void* out_final_commitment64, void* out_round_commitment64, char* error_msg,
+                              unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !wtns_signals || !out_A64 || !out_B128 || !out_final_commitment64 || !out_round_commitment64)
+        throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    if (!b->is_ultra()) throw std::invalid_argument("not an ultragroth prover");
+    UltraGrothProver::Lookup lk;
+    lk.chunks = chunks; lk.freqs = frequencies; lk.widx = wtns_indxs; lk.pidx = push_indxs;
+    lk.chunks_len = chunks_len; lk.freqs_len = frequencies_len; lk.idx_len = wtns_indxs_len;
+    HG1Affine A, C, R;
+    HG2Affine B;
+    static_cast<UltraGrothProver*>(b)->prove_raw((const uint8_t*)wtns_signals, lk, A, B, C, R, (uint8_t*)wtns_signals);
+    memcpy(out_A64, &A, 64); memcpy(out_B128, &B, 128); memcpy(out_final_commitment64, &C, 64); memcpy(out_round_commitment64, &R, 64);
+    API_CATCH_PROVE
+}
+
 // ---- point-range sharded proving (declared in include/ultragroth_b200.h) ---------
 // One prover object per GPU/process holds slice `rank` of `world` of every base array.  The MSM partial sums are
 // plain host structs (ugb_prover_partial_size() bytes) that the caller exchanges (NCCL / gloo all-gather, or a
@@ -636,6 +835,7 @@ int ugb_groth16_prove_partial(void* prover_object, const void* wtns_buffer, unsi
     API_TRY
     if (!prover_object || !wtns_buffer || !partial_out) throw std::invalid_argument("Null argument");
     ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
     if (b->is_ultra()) throw std::invalid_argument("not a groth16 prover");
     ProofMsms m;
     static_cast<Groth16Prover*>(b)->msms(wtns_buffer, wtns_size, m);
@@ -650,6 +850,7 @@ int ugb_groth16_prove_assemble(void* prover_object, const void* partials, uint32
     if (!prover_object || !partials || !wtns_buffer || !proof_buffer || !proof_size || !public_buffer || !public_size)
         throw std::invalid_argument("Null argument");
     ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
     if (b->is_ultra()) throw std::invalid_argument("not a groth16 prover");
     Groth16Prover* prover = static_cast<Groth16Prover*>(b);
     CheckAndUpdateBufferSizes(prover->proofBufferMinSize(), proof_size, prover->publicBufferMinSize(), public_size, "Minimum");
@@ -670,6 +871,7 @@ int ugb_ultra_round_partial(void* prover_object, const void* wtns_buffer, unsign
     API_TRY
     if (!prover_object || !wtns_buffer || !round_partial_out) throw std::invalid_argument("Null argument");
     ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
     if (!b->is_ultra()) throw std::invalid_argument("not an ultragroth prover");
     UltraGrothProver* prover = static_cast<UltraGrothProver*>(b);
     BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
@@ -688,6 +890,7 @@ int ugb_ultra_final_partial(void* prover_object, const void* wtns_buffer, unsign
     API_TRY
     if (!prover_object || !wtns_buffer || !round_partials || !rk32 || !partial_out || count == 0) throw std::invalid_argument("Null argument");
     ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
     if (!b->is_ultra()) throw std::invalid_argument("not an ultragroth prover");
     UltraGrothProver* prover = static_cast<UltraGrothProver*>(b);
     BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
@@ -701,7 +904,7 @@ int ugb_ultra_final_partial(void* prover_object, const void* wtns_buffer, unsign
     memcpy(&rk, rk32, 32);
     HG1Affine commit_aff;
     ProofMsms m;
-    prover->final_msms(commit, rk, lk, commit_aff, m);
+    prover->final_msms(commit, rk, &lk, commit_aff, m);
     m.round_c = XYZZ<HFq>::from_affine(commit_aff);  // the blinded commitment, identical on every shard
     memcpy(partial_out, &m, sizeof(m));
     API_CATCH_PROVE
@@ -714,6 +917,7 @@ int ugb_ultra_prove_assemble(void* prover_object, const void* partials, uint32_t
     if (!prover_object || !partials || !rk32 || !proof_buffer || !proof_size || !public_buffer || !public_size || count == 0)
         throw std::invalid_argument("Null argument");
     ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
     if (!b->is_ultra()) throw std::invalid_argument("not an ultragroth prover");
     UltraGrothProver* prover = static_cast<UltraGrothProver*>(b);
     CheckAndUpdateBufferSizes(prover->proofBufferMinSize(), proof_size, prover->publicBufferMinSize(), public_size, "Minimum");

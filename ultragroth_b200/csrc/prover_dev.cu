@@ -4,7 +4,9 @@
 #include "prover_dev.hpp"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
+#include <thread>
 
 #include "curve.cuh"
 #include "memops.cuh"
@@ -122,26 +124,39 @@ __global__ void __launch_bounds__(128) k_lookup_inverses(const uint32_t* __restr
             r = fp_mul(inv, pre[k]);
             inv = fp_mul(inv, val[k]);
         }
+        // the reference converts the uint32_t frequency to `int` (build/fr.hpp:251 -> RawFr::set(int), build/fr.cpp:209-223):
+        // a frequency >= 2^31 is the NEGATIVE number f - 2^32, i.e. -(2^32 - f) mod r
+        const uint32_t fv = freqs[base + k];
         Fr f = Fr::zero();
-        f.v[0] = freqs[base + k];
+        f.v[0] = (fv >> 31) ? 0u - fv : fv;
+        f = fp_to_mont(f);
+        if (fv >> 31) f = fp_neg(f);
         st_g(&inv2[base + k], fp_from_mont(r));
-        st_g(&prod[base + k], fp_from_mont(fp_mul(fp_to_mont(f), r)));
+        st_g(&prod[base + k], fp_from_mont(fp_mul(f, r)));
     }
 }
 
 // signals[wtns_idx[k]] = push_vector[push_idx[k]], push_vector = [rand | inv2[chunks[*]] | inv2 | prod]
+// The reference trusts the four index arrays (out-of-range entries are wild reads / writes there); here every index is checked where
+// it is used and a violation sets *err (1: witness index, 2: push index, 4: chunk value) instead of touching memory; the host turns
+// a non-zero flag into a std::range_error once the proof's results arrive.
 __global__ void __launch_bounds__(256) k_lookup_push(const uint32_t* __restrict__ wtns_idx, const uint32_t* __restrict__ push_idx,
                                                      uint32_t count, const uint32_t* __restrict__ chunks, uint32_t chunks_total,
-                                                     uint32_t lookup_size, Fr rand_raw, const Fr* __restrict__ inv2,
-                                                     const Fr* __restrict__ prod, Fr* __restrict__ signals) {
+                                                     uint32_t lookup_size, uint32_t n_vars, Fr rand_raw, const Fr* __restrict__ inv2,
+                                                     const Fr* __restrict__ prod, Fr* __restrict__ signals, uint32_t* __restrict__ err) {
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) {
-        uint32_t p = push_idx[k];
+        const uint32_t p = push_idx[k], wi = wtns_idx[k];
+        if (wi >= n_vars) { atomicOr(err, 1u); continue; }
         Fr v;
         if (p == 0) v = rand_raw;
-        else if (p <= chunks_total) v = ld_g(&inv2[chunks[p - 1]]);
-        else if (p <= chunks_total + lookup_size) v = ld_g(&inv2[p - 1 - chunks_total]);
-        else v = ld_g(&prod[p - 1 - chunks_total - lookup_size]);
-        st_g(&signals[wtns_idx[k]], v);
+        else if (p <= chunks_total) {
+            const uint32_t ch = chunks[p - 1];
+            if (ch >= lookup_size) { atomicOr(err, 4u); continue; }
+            v = ld_g(&inv2[ch]);
+        } else if ((uint64_t)p <= (uint64_t)chunks_total + lookup_size) v = ld_g(&inv2[p - 1 - chunks_total]);
+        else if ((uint64_t)p <= (uint64_t)chunks_total + 2ull * lookup_size) v = ld_g(&prod[p - 1 - chunks_total - lookup_size]);
+        else { atomicOr(err, 2u); continue; }
+        st_g(&signals[wi], v);
     }
 }
 
@@ -165,35 +180,160 @@ static int ilog2_exact(uint32_t n) {
     return k;
 }
 
-ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h, uint32_t shard_rank, uint32_t shard_world, bool tables)
-    : nVars(h.nVars), nPublic(h.nPublic), domainSize(h.domainSize), ultra_(h.ultra) {
-    if (shard_world == 0 || shard_rank >= shard_world) throw std::invalid_argument("bad shard rank / world");
-    shard_range(nVars, shard_world, shard_rank, w_lo_, w_hi_);
-    shard_range(domainSize, shard_world, shard_rank, h_lo_, h_hi_);
-    const uint64_t wn = w_hi_ - w_lo_, hn = h_hi_ - h_lo_;
+ZkeyData zkey_data_from_file(const BinFile& zkey, const ZkeyHeader& h) {
+    ZkeyData z;
+    z.ultra = h.ultra;
+    z.nVars = h.nVars; z.nPublic = h.nPublic; z.domainSize = h.domainSize;
     if (h.n8q != 32 || h.n8r != 32) throw std::invalid_argument("zkey field size not supported");
+    auto sec = [&](uint32_t id, const uint8_t*& p, uint64_t& bytes) { p = zkey.data(id); bytes = zkey.size(id); };
+    {
+        const uint64_t sec_size = zkey.size(4);
+        if (sec_size < 4) throw std::range_error("zkey section too short: coefs");
+        z.coefs = zkey.data(4) + 4;
+        z.coefs_bytes = sec_size - 4;
+        z.nCoefs = std::min<uint64_t>(h.nCoefs, (sec_size - 4) / 44);
+    }
+    sec(5, z.A, z.A_bytes); sec(6, z.B1, z.B1_bytes); sec(7, z.B2, z.B2_bytes);
+    if (!h.ultra) {
+        sec(8, z.C, z.C_bytes); sec(9, z.H, z.H_bytes);
+    } else {
+        z.n_c1 = h.num_indexes_c1; z.n_c2 = h.num_indexes_c2;
+        sec(8, z.C1, z.C1_bytes); sec(9, z.C, z.C_bytes); sec(10, z.idx_c1, z.idx_c1_bytes); sec(11, z.idx_c2, z.idx_c2_bytes); sec(12, z.H, z.H_bytes);
+    }
+    return z;
+}
+
+// out[idx[i] - lo] = in[i] for idx[i] in [lo, hi): places the final-round C points at their witness slots
+__global__ void __launch_bounds__(256) k_scatter_affine(const G1Affine* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t count, uint32_t lo,
+                                                        uint32_t hi, G1Affine* __restrict__ out) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const uint32_t s = idx[i];
+        if (s >= lo && s < hi) st_g(&out[s - lo], ld_nc(&in[i]));
+    }
+}
+
+namespace {
+double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// Packed coefficient records -> CSR by (matrix, row), built by `nthreads` host threads.  Thread t owns the slots (m*n + c) of one
+// contiguous range and scans ALL records for them, so the layout is deterministic (record order inside a row is kept) and no
+// two threads ever write the same counter.
+struct CoefCsr {
+    std::vector<uint32_t> rp, sig;
+    std::vector<uint8_t> val;
+    std::vector<LongRow> longs, segs;
+};
+void build_csr(const ZkeyData& zk, CoefCsr& out) {
+    const uint32_t n = zk.domainSize, nVars = zk.nVars;
+    const uint64_t cnt = zk.nCoefs;
+    const uint8_t* rec = zk.coefs;
+    const size_t slots = (size_t)2 * n;
+    unsigned hw = std::thread::hardware_concurrency();
+    const int nthreads = (int)std::max<uint64_t>(1, std::min<uint64_t>({(uint64_t)(hw ? hw : 4), 32, cnt / 65536 + 1}));
+    std::vector<uint32_t> len(slots, 0);
+    std::vector<std::string> errs(nthreads);
+    auto run = [&](auto fn) {
+        std::vector<std::thread> th;
+        for (int t = 1; t < nthreads; t++) th.emplace_back(fn, t);
+        fn(0);
+        for (auto& x : th) x.join();
+        for (auto& e : errs) if (!e.empty()) throw std::range_error(e);
+    };
+    auto range = [&](int t, size_t& lo, size_t& hi) { lo = slots * t / nthreads; hi = slots * (t + 1) / nthreads; };
+    run([&](int t) {
+        size_t lo, hi;
+        range(t, lo, hi);
+        for (uint64_t k = 0; k < cnt; k++) {
+            uint32_t m, c, s;
+            memcpy(&m, rec + k * 44, 4); memcpy(&c, rec + k * 44 + 4, 4); memcpy(&s, rec + k * 44 + 8, 4);
+            if (m > 1 || c >= n || s >= nVars) { if (t == 0) errs[0] = "zkey coefficient record out of range"; continue; }
+            const size_t slot = (size_t)m * n + c;
+            if (slot >= lo && slot < hi) len[slot]++;
+        }
+    });
+    // short rows form the CSR proper; long rows keep an empty CSR row and live after `short_total`
+    out.rp.assign(slots + 1, 0);
+    for (size_t i = 0; i < slots; i++) out.rp[i + 1] = out.rp[i] + (len[i] > SPMV_LONG_ROW ? 0 : len[i]);
+    uint32_t tail = out.rp[slots];
+    std::vector<uint32_t> cur(out.rp.begin(), out.rp.end() - 1);
+    for (size_t i = 0; i < slots; i++) {
+        if (len[i] > SPMV_LONG_ROW) {
+            const uint32_t seg0 = (uint32_t)out.segs.size();
+            for (uint32_t o = 0; o < len[i]; o += SPMV_SEG) out.segs.push_back(LongRow{(uint32_t)i, tail + o, tail + std::min(len[i], o + SPMV_SEG)});
+            out.longs.push_back(LongRow{(uint32_t)i, seg0, (uint32_t)out.segs.size()});
+            cur[i] = tail;
+            tail += len[i];
+        }
+    }
+    out.sig.resize(cnt);
+    out.val.resize(cnt * 32);
+    run([&](int t) {
+        size_t lo, hi;
+        range(t, lo, hi);
+        for (uint64_t k = 0; k < cnt; k++) {
+            uint32_t m, c, s;
+            memcpy(&m, rec + k * 44, 4); memcpy(&c, rec + k * 44 + 4, 4); memcpy(&s, rec + k * 44 + 8, 4);
+            const size_t slot = (size_t)m * n + c;
+            if (slot < lo || slot >= hi) continue;
+            const uint32_t pos = cur[slot]++;
+            out.sig[pos] = s;
+            memcpy(&out.val[(size_t)pos * 32], rec + k * 44 + 12, 32);
+        }
+    });
+}
+}  // namespace
+
+ProverDevice::ProverDevice(int device, const ZkeyData& zk, uint32_t shard_rank, uint32_t shard_world, bool tables)
+    : nVars(zk.nVars), nPublic(zk.nPublic), domainSize(zk.domainSize), ultra_(zk.ultra) {
+    if (shard_world == 0 || shard_rank >= shard_world) throw std::invalid_argument("bad shard rank / world");
     logn = ilog2_exact(domainSize);
     if (nPublic + 1 > nVars) throw std::invalid_argument("zkey header is inconsistent (nPublic >= nVars)");
     ctx_.reset(new DeviceCtx(device));
+    // every device buffer below is a raw cudaMalloc pointer: a throw half way through must not leak them (a server that
+    // retries *_prover_create on bad or oversized zkeys would exhaust HBM)
+    try {
+        construct(zk, shard_rank, shard_world, tables);
+    } catch (...) {
+        release();
+        throw;
+    }
+}
+
+void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t shard_world, bool tables) {
+    const double t_begin = now_ms();
+    shard_range(nVars, shard_world, shard_rank, w_lo_, w_hi_);
+    shard_range(domainSize, shard_world, shard_rank, h_lo_, h_hi_);
+    const uint64_t wn = w_hi_ - w_lo_, hn = h_hi_ - h_lo_;
     tabs_.reset(new NttTables(*ctx_));
     DeviceCtx& ctx = *ctx_;
     ctx.activate();
     timing = getenv("UGB_TIMING") != nullptr;
 
-    auto need = [&](uint32_t id, uint64_t bytes, const char* what) {
-        if (zkey.size(id) < bytes) throw std::range_error(std::string("zkey section too short: ") + what);
+    auto need = [&](uint64_t have, uint64_t bytes, const char* what) {
+        if (have < bytes) throw std::range_error(std::string("zkey section too short: ") + what);
     };
-    need(5, (uint64_t)nVars * 64, "pointsA");
-    need(6, (uint64_t)nVars * 64, "pointsB1");
-    need(7, (uint64_t)nVars * 128, "pointsB2");
-    A_ = upload(ctx, zkey.data(5) + w_lo_ * 64, (size_t)wn * 64);
-    B1_ = upload(ctx, zkey.data(6) + w_lo_ * 64, (size_t)wn * 64);
-    B2_ = upload(ctx, zkey.data(7) + w_lo_ * 128, (size_t)wn * 128);
-    std::vector<uint8_t> cfull;  // must outlive the async copy
+    need(zk.coefs_bytes, zk.nCoefs * 44, "coefs");
+    need(zk.A_bytes, (uint64_t)nVars * 64, "pointsA");
+    need(zk.B1_bytes, (uint64_t)nVars * 64, "pointsB1");
+    need(zk.B2_bytes, (uint64_t)nVars * 128, "pointsB2");
+    need(zk.H_bytes, (uint64_t)domainSize * 64, "pointsH");
+    // the coefficient CSR is host work: it runs on its own threads while the bases are uploaded and the window tables are built
+    CoefCsr csr;
+    std::string csr_err;
+    double csr_ms = 0;
+    std::thread csr_thread([&]() {
+        const double t0 = now_ms();
+        try { build_csr(zk, csr); } catch (std::exception& e) { csr_err = e.what(); if (csr_err.empty()) csr_err = "coefficient CSR build failed"; }
+        csr_ms = now_ms() - t0;
+    });
+    struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } joiner{csr_thread};
+
+    A_ = upload(ctx, zk.A + w_lo_ * 64, (size_t)wn * 64);
+    B1_ = upload(ctx, zk.B1 + w_lo_ * 64, (size_t)wn * 64);
+    B2_ = upload(ctx, zk.B2 + w_lo_ * 128, (size_t)wn * 128);
     if (!ultra_) {
         const uint32_t nc = nVars - nPublic - 1;
-        need(8, (uint64_t)nc * 64, "pointsC");
-        need(9, (uint64_t)domainSize * 64, "pointsH");
+        need(zk.C_bytes, (uint64_t)nc * 64, "pointsC");
         // C pairs with witness[nPublic+1 ..] (src/groth16.cpp:64): pad with points at infinity so that the
         // C MSM reuses the sorted digits of the full witness
         // slot i of the padded array = pointsC[i - (nPublic+1)] for i > nPublic, infinity below; keep [w_lo_, w_hi_)
@@ -202,106 +342,60 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h,
         {
             const uint64_t first = std::max<uint64_t>(w_lo_, (uint64_t)nPublic + 1);
             if (first < w_hi_)
-                UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)C_ + (first - w_lo_) * 64, zkey.data(8) + (first - nPublic - 1) * 64, (size_t)(w_hi_ - first) * 64, cudaMemcpyHostToDevice, ctx.stream));
+                UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)C_ + (first - w_lo_) * 64, zk.C + (first - nPublic - 1) * 64, (size_t)(w_hi_ - first) * 64, cudaMemcpyHostToDevice, ctx.stream));
         }
         c_shares_witness_sort_ = true;
-        H_ = upload(ctx, zkey.data(9) + h_lo_ * 64, (size_t)hn * 64);
+        H_ = upload(ctx, zk.H + h_lo_ * 64, (size_t)hn * 64);
     } else {
-        n_c1_ = h.num_indexes_c1;
-        n_c2_ = h.num_indexes_c2;
-        need(8, (uint64_t)n_c1_ * 64, "round pointsC");
-        need(9, (uint64_t)n_c2_ * 64, "final pointsC");
-        need(10, (uint64_t)n_c1_ * 4, "round indexes");
-        need(11, (uint64_t)n_c2_ * 4, "final indexes");
-        need(12, (uint64_t)domainSize * 64, "pointsH");
-        const uint32_t* i1 = (const uint32_t*)zkey.data(10);
-        const uint32_t* i2 = (const uint32_t*)zkey.data(11);
-        for (uint32_t i = 0; i < n_c1_; i++) { uint32_t v; memcpy(&v, i1 + i, 4); if (v >= nVars) throw std::range_error("round index out of range"); }
+        n_c1_ = zk.n_c1;
+        n_c2_ = zk.n_c2;
+        need(zk.C1_bytes, (uint64_t)n_c1_ * 64, "round pointsC");
+        need(zk.C_bytes, (uint64_t)n_c2_ * 64, "final pointsC");
+        need(zk.idx_c1_bytes, (uint64_t)n_c1_ * 4, "round indexes");
+        need(zk.idx_c2_bytes, (uint64_t)n_c2_ * 4, "final indexes");
+        const uint8_t* i1 = zk.idx_c1;
+        const uint8_t* i2 = zk.idx_c2;
+        for (uint32_t i = 0; i < n_c1_; i++) { uint32_t v; memcpy(&v, i1 + (size_t)i * 4, 4); if (v >= nVars) throw std::range_error("round index out of range"); }
         bool unique = true;
         {
             std::vector<bool> seen(nVars, false);
             for (uint32_t i = 0; i < n_c2_; i++) {
-                uint32_t v; memcpy(&v, i2 + i, 4);
+                uint32_t v; memcpy(&v, i2 + (size_t)i * 4, 4);
                 if (v >= nVars) throw std::range_error("final round index out of range");
                 if (seen[v]) unique = false;
                 seen[v] = true;
             }
         }
         shard_range(n_c1_, shard_world, shard_rank, c1_lo_, c1_hi_);
-        C1_ = upload(ctx, zkey.data(8) + c1_lo_ * 64, (size_t)(c1_hi_ - c1_lo_) * 64);
-        idx_c1_ = (uint32_t*)upload(ctx, zkey.data(10), (size_t)n_c1_ * 4);
-        idx_c2_ = (uint32_t*)upload(ctx, zkey.data(11), (size_t)n_c2_ * 4);
+        C1_ = upload(ctx, zk.C1 + c1_lo_ * 64, (size_t)(c1_hi_ - c1_lo_) * 64);
+        idx_c1_ = (uint32_t*)upload(ctx, zk.idx_c1, (size_t)n_c1_ * 4);
+        idx_c2_ = (uint32_t*)upload(ctx, zk.idx_c2, (size_t)n_c2_ * 4);
         if (unique) {
             // final_wtns[i] = wtns[final_idx[i]] (src/ultra_groth.cpp:439-445): place C2[i] at slot final_idx[i]
-            // of an nVars-long array of points at infinity, so the final C MSM shares the witness digits
-            cfull.assign((size_t)nVars * 64, 0);
-            const uint8_t* c2 = zkey.data(9);
-            for (uint32_t i = 0; i < n_c2_; i++) { uint32_t v; memcpy(&v, i2 + i, 4); memcpy(&cfull[(size_t)v * 64], c2 + (size_t)i * 64, 64); }
-            C_ = upload(ctx, cfull.data() + w_lo_ * 64, (size_t)wn * 64);
+            // of an nVars-long array of points at infinity, so the final C MSM shares the witness digits (scatter on the device)
+            void* c2 = upload(ctx, zk.C, (size_t)n_c2_ * 64);
+            C_ = dev_alloc((size_t)wn * 64);
+            UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, std::max<size_t>((size_t)wn * 64, 16), ctx.stream));
+            if (n_c2_) {
+                const int blocks = (int)std::min<uint64_t>(((uint64_t)n_c2_ + 255) / 256, (uint64_t)ctx.sm_count * 8);
+                UG_KERNEL(ctx, "k_scatter_affine", k_scatter_affine<<<blocks, 256, 0, ctx.stream>>>((const G1Affine*)c2, idx_c2_, n_c2_, (uint32_t)w_lo_, (uint32_t)w_hi_, (G1Affine*)C_));
+            }
+            UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+            UG_CUDA_CHECK(cudaFree(c2));
             c_shares_witness_sort_ = true;
         } else {
             if (shard_world > 1) throw std::invalid_argument("sharded UltraGroth prover needs unique final-round indexes");
-            C_ = upload(ctx, zkey.data(9), (size_t)n_c2_ * 64);
+            C_ = upload(ctx, zk.C, (size_t)n_c2_ * 64);
             c_shares_witness_sort_ = false;
         }
-        H_ = upload(ctx, zkey.data(12) + h_lo_ * 64, (size_t)hn * 64);
+        H_ = upload(ctx, zk.H + h_lo_ * 64, (size_t)hn * 64);
     }
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+    create_ms[0] = now_ms() - t_begin;
 
-    // coefficient records {u32 m, u32 c, u32 s, Fr coef} packed(1) after a u32 count (src/groth16.cpp:38,
-    // src/groth16.hpp:42-50) -> CSR by (m, c)
-    {
-        const uint8_t* sec = zkey.data(4);
-        uint64_t sec_size = zkey.size(4);
-        if (sec_size < 4) throw std::range_error("zkey section too short: coefs");
-        uint64_t cnt = std::min<uint64_t>(h.nCoefs, (sec_size - 4) / 44);
-        const uint8_t* rec = sec + 4;
-        nCoefs_ = cnt;
-        const uint32_t n = domainSize;
-        std::vector<uint32_t> len((size_t)2 * n, 0);
-        for (uint64_t k = 0; k < cnt; k++) {
-            uint32_t m, c, s;
-            memcpy(&m, rec + k * 44, 4); memcpy(&c, rec + k * 44 + 4, 4); memcpy(&s, rec + k * 44 + 8, 4);
-            if (m > 1 || c >= n || s >= nVars) throw std::range_error("zkey coefficient record out of range");
-            len[(size_t)m * n + c]++;
-        }
-        // short rows form the CSR proper; long rows keep an empty CSR row and live after `short_total`
-        std::vector<uint32_t> rp((size_t)2 * n + 1, 0);
-        std::vector<LongRow> longs, segs;
-        for (size_t i = 0; i < (size_t)2 * n; i++) rp[i + 1] = rp[i] + (len[i] > SPMV_LONG_ROW ? 0 : len[i]);
-        uint32_t tail = rp[(size_t)2 * n];
-        std::vector<uint32_t> cur(rp.begin(), rp.end() - 1);
-        for (size_t i = 0; i < (size_t)2 * n; i++) {
-            if (len[i] > SPMV_LONG_ROW) {
-                const uint32_t seg0 = (uint32_t)segs.size();
-                for (uint32_t o = 0; o < len[i]; o += SPMV_SEG) segs.push_back(LongRow{(uint32_t)i, tail + o, tail + std::min(len[i], o + SPMV_SEG)});
-                longs.push_back(LongRow{(uint32_t)i, seg0, (uint32_t)segs.size()});
-                cur[i] = tail;
-                tail += len[i];
-            }
-        }
-        std::vector<uint32_t> sig(cnt);
-        std::vector<uint8_t> val(cnt * 32);
-        for (uint64_t k = 0; k < cnt; k++) {
-            uint32_t m, c, s;
-            memcpy(&m, rec + k * 44, 4); memcpy(&c, rec + k * 44 + 4, 4); memcpy(&s, rec + k * 44 + 8, 4);
-            uint32_t pos = cur[(size_t)m * n + c]++;
-            sig[pos] = s;
-            memcpy(&val[(size_t)pos * 32], rec + k * 44 + 12, 32);
-        }
-        n_long_ = (uint32_t)longs.size();
-        n_long_segs_ = (uint32_t)segs.size();
-        if (n_long_) {
-            long_rows_ = upload(ctx, longs.data(), longs.size() * sizeof(LongRow));
-            long_segs_ = upload(ctx, segs.data(), segs.size() * sizeof(LongRow));
-            long_partial_ = dev_alloc((size_t)n_long_segs_ * 32);
-        }
-        row_ptr_ = (uint32_t*)upload(ctx, rp.data(), rp.size() * 4);
-        coef_sig_ = (uint32_t*)upload(ctx, sig.data(), sig.size() * 4);
-        coef_val_ = upload(ctx, val.data(), val.size());
-        UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
-    }
     // window tables: 2^(c*w) multiples of every base, resident next to the bases they replace (UGB_MSM_PRE=0: off)
     {
+        const double t0 = now_ms();
         const char* e = getenv("UGB_MSM_PRE");
         pre_ = tables && !(e && atoi(e) == 0);
         if (pre_) {
@@ -320,7 +414,25 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h,
             tabulate(H_, 1, hn, cfg_h_);
             if (ultra_) tabulate(C1_, 1, c1_hi_ - c1_lo_, cfg_c1_);
         }
+        create_ms[2] = now_ms() - t0;
     }
+    // coefficient records {u32 m, u32 c, u32 s, Fr coef} packed(1) (src/groth16.cpp:38, src/groth16.hpp:42-50) -> CSR by (m, c)
+    csr_thread.join();
+    if (!csr_err.empty()) throw std::range_error(csr_err);
+    create_ms[1] = csr_ms;
+    nCoefs_ = zk.nCoefs;
+    n_long_ = (uint32_t)csr.longs.size();
+    n_long_segs_ = (uint32_t)csr.segs.size();
+    if (n_long_) {
+        long_rows_ = upload(ctx, csr.longs.data(), csr.longs.size() * sizeof(LongRow));
+        long_segs_ = upload(ctx, csr.segs.data(), csr.segs.size() * sizeof(LongRow));
+        long_partial_ = dev_alloc((size_t)n_long_segs_ * 32);
+    }
+    row_ptr_ = (uint32_t*)upload(ctx, csr.rp.data(), csr.rp.size() * 4);
+    coef_sig_ = (uint32_t*)upload(ctx, csr.sig.data(), csr.sig.size() * 4);
+    coef_val_ = upload(ctx, csr.val.data(), csr.val.size());
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+
     w_ = dev_alloc((size_t)nVars * 32);
     a_ = dev_alloc((size_t)domainSize * 32);
     b_ = dev_alloc((size_t)domainSize * 32);
@@ -335,15 +447,22 @@ ProverDevice::ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& h,
     ev_.resize(16);
     for (auto& e : ev_) UG_CUDA_CHECK(cudaEventCreate(&e));
     UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+    create_ms[3] = now_ms() - t_begin;
 }
 
-ProverDevice::~ProverDevice() {
+void ProverDevice::release() {
+    if (!ctx_) return;
     cudaSetDevice(ctx_->device);
     cudaStreamSynchronize(ctx_->stream);
-    for (void* p : {long_rows_, long_segs_, long_partial_, A_, B1_, B2_, C_, H_, C1_, (void*)idx_c1_, (void*)idx_c2_, (void*)row_ptr_, (void*)coef_sig_, coef_val_, w_, a_, b_, c_})
-        if (p) cudaFree(p);
-    for (auto& e : ev_) cudaEventDestroy(e);
+    void** ptrs[] = {&long_rows_, &long_segs_, &long_partial_, &A_, &B1_, &B2_, &C_, &H_, &C1_, (void**)&idx_c1_, (void**)&idx_c2_, (void**)&row_ptr_,
+                     (void**)&coef_sig_, &coef_val_, &w_, &a_, &b_, &c_};
+    for (void** p : ptrs) if (*p) { cudaFree(*p); *p = nullptr; }
+    for (auto& e : ev_) if (e) cudaEventDestroy(e);
+    ev_.clear();
+    cudaGetLastError();
 }
+
+ProverDevice::~ProverDevice() { release(); }
 
 void ProverDevice::download_h(std::vector<uint8_t>& out) {
     ctx_->activate();
@@ -422,6 +541,7 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
     msm_g2_finish(ctx, dw, "b2", &out.b2);
     msm_g1_finish(ctx, c_shares_witness_sort_ ? dw : dc, "c", &out.c);
     msm_g1_finish(ctx, dh, "h", &out.h);
+    check_lookup_error();  // the flag travelled before the MSM results on the same stream
     ctx.prof_collect();
     if (timing) {
         UG_CUDA_CHECK(cudaEventSynchronize(ev_[11]));
@@ -464,17 +584,12 @@ void ProverDevice::ultra_round_msm(HG1XYZZ& out) {
     msm_g1_finish(ctx, d, "round", &out);
 }
 
-void ProverDevice::ultra_lookup_stage(const uint32_t* chunks, uint32_t chunks_len, const uint32_t* freqs, uint32_t freqs_len,
-                                      const uint32_t* wtns_idx, const uint32_t* push_idx, uint32_t idx_len) {
+void ProverDevice::ultra_lookup_stage(const void* chunks, uint32_t chunks_len, const void* freqs, uint32_t freqs_len,
+                                      const void* wtns_idx, const void* push_idx, uint32_t idx_len) {
     DeviceCtx& ctx = *ctx_;
     ctx.activate();
-    // bounds (the reference trusts the file; out-of-range indices would be wild writes there)
-    for (uint32_t i = 0; i < chunks_len; i++) if (chunks[i] >= freqs_len) throw std::range_error("lookup chunk index out of range");
-    const uint64_t push_len = 1ull + chunks_len + 2ull * freqs_len;
-    for (uint32_t i = 0; i < idx_len; i++) {
-        if (wtns_idx[i] >= nVars) throw std::range_error("lookup witness index out of range");
-        if (push_idx[i] >= push_len) throw std::range_error("lookup push index out of range");
-    }
+    // straight copies on the proof's stream (the caller's arrays are borrowed until the proof's final synchronisation); all range
+    // checks happen on the device, where the indices are used (k_lookup_push)
     uint32_t* d_chunks = (uint32_t*)ctx.workspace("lk.chunks", (size_t)chunks_len * 4 + 16);
     uint32_t* d_freqs = (uint32_t*)ctx.workspace("lk.freqs", (size_t)freqs_len * 4 + 16);
     uint32_t* d_widx = (uint32_t*)ctx.workspace("lk.widx", (size_t)idx_len * 4 + 16);
@@ -498,6 +613,9 @@ void ProverDevice::ultra_lookup_apply(const HFr& rand_mont) {
     uint32_t* d_pidx = (uint32_t*)ctx.workspace("lk.pidx", (size_t)idx_len * 4 + 16);
     Fr* d_inv2 = (Fr*)ctx.workspace("lk.inv2", (size_t)freqs_len * 32 + 32);
     Fr* d_prod = (Fr*)ctx.workspace("lk.prod", (size_t)freqs_len * 32 + 32);
+    uint32_t* d_err = (uint32_t*)ctx.workspace("lk.err", 16);
+    uint32_t* h_err = (uint32_t*)ctx.pinned("lk.err", 16);
+    UG_CUDA_CHECK(cudaMemsetAsync(d_err, 0, 4, ctx.stream));
     Fr rm, rr;
     memcpy(&rm, &rand_mont, 32);
     HFr raw = from_mont(rand_mont);
@@ -508,9 +626,19 @@ void ProverDevice::ultra_lookup_apply(const HFr& rand_mont) {
     }
     if (idx_len) {
         int blocks = (int)std::min<uint64_t>(((uint64_t)idx_len + 255) / 256, (uint64_t)ctx.sm_count * 8);
-        UG_KERNEL(ctx, "k_lookup_push", k_lookup_push<<<blocks, 256, 0, ctx.stream>>>(d_widx, d_pidx, idx_len, d_chunks, chunks_len, freqs_len, rr, d_inv2, d_prod, (Fr*)w_));
+        UG_KERNEL(ctx, "k_lookup_push", k_lookup_push<<<blocks, 256, 0, ctx.stream>>>(d_widx, d_pidx, idx_len, d_chunks, chunks_len, freqs_len, nVars, rr, d_inv2, d_prod, (Fr*)w_, d_err));
     }
-    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));  // the staged host index arrays are borrowed until here
+    UG_CUDA_CHECK(cudaMemcpyAsync(h_err, d_err, 4, cudaMemcpyDeviceToHost, ctx.stream));
+    lookup_err_pending_ = true;
+}
+
+void ProverDevice::check_lookup_error() {
+    if (!lookup_err_pending_) return;
+    lookup_err_pending_ = false;
+    const uint32_t e = *(const uint32_t*)ctx_->pinned("lk.err", 16);
+    if (e & 1u) throw std::range_error("lookup witness index out of range");
+    if (e & 2u) throw std::range_error("lookup push index out of range");
+    if (e & 4u) throw std::range_error("lookup chunk index out of range");
 }
 
 void ProverDevice::ultra_final_msms(ProofMsms& out) {

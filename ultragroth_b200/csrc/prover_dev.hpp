@@ -26,19 +26,37 @@ struct StageTimes {  // milliseconds of device time per stage of the last proof 
           hfinal = 0, sort_h = 0, msm_h = 0, total = 0;
 };
 
+// What the device prover needs from a zkey: borrowed HOST pointers, valid only during ProverDevice construction.  Filled either
+// from a parsed zkey file (zkey_data_from_file: the section casts of src/prover.cpp:160-189,237-260) or from the section
+// pointers a C++ embedder hands to Groth16::makeProver / UltraGroth::makeProver (src/groth16.hpp:118-136, src/ultra_groth.hpp:218-247).
+// *_bytes: how many bytes are readable behind the pointer (SIZE_MAX = trusted, as the reference's class API trusts its caller).
+struct ZkeyData {
+    bool ultra = false;
+    uint32_t nVars = 0, nPublic = 0, domainSize = 0;
+    uint64_t nCoefs = 0;
+    const uint8_t* coefs = nullptr;  // nCoefs packed 44-byte records {u32 m, u32 c, u32 s, Fr coef} (after the u32 count of section 4)
+    const uint8_t *A = nullptr, *B1 = nullptr, *B2 = nullptr, *C = nullptr /* Groth16 C / UltraGroth final C */, *H = nullptr, *C1 = nullptr /* round C */;
+    const uint8_t *idx_c1 = nullptr, *idx_c2 = nullptr;  // u32 lists (UltraGroth)
+    uint32_t n_c1 = 0, n_c2 = 0;
+    uint64_t coefs_bytes = UINT64_MAX, A_bytes = UINT64_MAX, B1_bytes = UINT64_MAX, B2_bytes = UINT64_MAX, C_bytes = UINT64_MAX, H_bytes = UINT64_MAX,
+             C1_bytes = UINT64_MAX, idx_c1_bytes = UINT64_MAX, idx_c2_bytes = UINT64_MAX;
+};
+ZkeyData zkey_data_from_file(const BinFile& zkey, const ZkeyHeader& hdr);
+
 class ProverDevice {
 public:
     // shard_rank / shard_world: point-range sharding: this device keeps only slice
     // shard_range(count, world, rank) of every base array resident and its MSMs return PARTIAL sums; the
     // witness, the coefficients and the H pipeline are replicated on every shard.
     // tables = false: skip the window-table build (one-shot *_prover calls: the 2^(c*k) multiples only pay off across proofs)
-    ProverDevice(int device, const BinFile& zkey, const ZkeyHeader& hdr, uint32_t shard_rank = 0, uint32_t shard_world = 1, bool tables = true);
+    ProverDevice(int device, const ZkeyData& zk, uint32_t shard_rank = 0, uint32_t shard_world = 1, bool tables = true);
     static void shard_range(uint64_t n, uint32_t world, uint32_t rank, uint64_t& lo, uint64_t& hi) {
         const uint64_t base = n / world, rem = n % world;
         lo = rank * base + std::min<uint64_t>(rank, rem);
         hi = lo + base + (rank < rem ? 1 : 0);
     }
     ~ProverDevice();
+    double create_ms[4] = {0, 0, 0, 0};  // create-time breakdown: base uploads, coefficient CSR, window tables, total
 
     DeviceCtx& ctx() { return *ctx_; }
     NttTables& tables() { return *tabs_; }
@@ -53,10 +71,11 @@ public:
     // ---- UltraGroth (src/ultra_groth.cpp:401-462) ----
     void ultra_upload_witness(const uint8_t* witness);
     void ultra_round_msm(HG1XYZZ& out);                                   // execute_round's MSM (:168)
-    // compute_lookup (:62-106) in two halves: _stage range-checks the four index arrays and copies them to HBM (asynchronous; the
-    // host arrays must stay valid until the next stream synchronisation), _apply runs the kernels once the challenge is known
-    void ultra_lookup_stage(const uint32_t* chunks, uint32_t chunks_len, const uint32_t* freqs, uint32_t freqs_len, const uint32_t* wtns_idx,
-                            const uint32_t* push_idx, uint32_t idx_len);
+    // compute_lookup (:62-106) in two halves: _stage copies the four u32 index arrays to HBM (asynchronous; the host arrays -- any
+    // alignment -- must stay valid until the proof's final synchronisation), _apply runs the kernels once the challenge is known;
+    // indices are range-checked on the device and a violation surfaces as std::range_error from ultra_final_msms
+    void ultra_lookup_stage(const void* chunks, uint32_t chunks_len, const void* freqs, uint32_t freqs_len, const void* wtns_idx,
+                            const void* push_idx, uint32_t idx_len);
     void ultra_lookup_apply(const HFr& rand_mont);
     void ultra_final_msms(ProofMsms& out);                                // execute_final_round's MSMs + H
     void download_witness(uint8_t* dst, uint64_t first, uint64_t count);  // signals after the lookup fill
@@ -70,7 +89,11 @@ public:
     int logn;
 
 private:
+    void construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t shard_world, bool tables);
+    void release();
     void h_pipeline_and_msms(ProofMsms& out, bool ultra);
+    void check_lookup_error();
+    bool lookup_err_pending_ = false;
     std::unique_ptr<DeviceCtx> ctx_;
     std::unique_ptr<NttTables> tabs_;
     bool ultra_;

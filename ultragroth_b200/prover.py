@@ -107,11 +107,40 @@ class Prover:
             raise ProverError(rc, "ugb_prover_last_h failed")
         return out.raw
 
+    MSM_NAMES = ("a", "b1", "b2", "c", "h", "round_c")
+
+    def last_msms(self):
+        """Raw MSM results of the last proof (before blinding / assembly) as affine Montgomery bytes in zkey layout:
+        {a, b1: 64 B; b2: 128 B; c, h, round_c: 64 B} (ugb_prover_last_msms)."""
+        out = ctypes.create_string_buffer(448)
+        rc = lib().ugb_prover_last_msms(self.handle, out)
+        if rc:
+            raise ProverError(rc, lib().ugb_last_error().decode(errors="replace"))
+        b = out.raw
+        return {"a": b[0:64], "b1": b[64:128], "b2": b[128:256], "c": b[256:320], "h": b[320:384], "round_c": b[384:448]}
+
+    def last_witness(self, first, count):
+        """`count` signals of the witness as it stands in HBM after the last proof (lookup signals filled in)."""
+        out = ctypes.create_string_buffer(32 * count)
+        rc = lib().ugb_prover_last_witness(self.handle, out, first, count)
+        if rc:
+            raise ProverError(rc, lib().ugb_last_error().decode(errors="replace"))
+        return out.raw
+
+    def create_times(self):
+        arr = (ctypes.c_double * 4)()
+        lib().ugb_prover_create_times(self.handle, arr)
+        return dict(zip(("upload_ms", "csr_ms", "tables_ms", "total_ms"), [float(x) for x in arr]))
+
     def prove_resident(self):
-        """Device part of a proof on the witness already in HBM (no host copies in)."""
+        """One whole proof from the witness (and lookup arrays) already in HBM: no host->device input copy.  -> (proof, public)"""
         rc = lib().ugb_prover_prove_resident(self.handle)
         if rc:
-            raise ProverError(rc, "ugb_prover_prove_resident failed")
+            raise ProverError(rc, lib().ugb_last_error().decode(errors="replace"))
+        proof = ctypes.create_string_buffer(self.proof_size + 1)
+        public = ctypes.create_string_buffer(self.public_size + 1)
+        lib().ugb_prover_last_proof(self.handle, proof, len(proof), public, len(public))
+        return proof.value.decode(), public.value.decode()
 
     def set_profile(self, on=True):
         lib().ugb_prover_set_profile(self.handle, 1 if on else 0)
