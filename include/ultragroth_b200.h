@@ -143,6 +143,13 @@ int ugb_ultra_groth_prove_raw(void* prover_object, void* wtns_signals, const uin
                               void* out_A64, void* out_B128, void* out_final_commitment64, void* out_round_commitment64, char* error_msg,
                               unsigned long long error_msg_maxsize);
 
+/* destroys a prover made by ugb_prover_create_from_sections (same as groth16_prover_destroy / ultra_groth_prover_destroy) */
+void ugb_prover_destroy(void* prover_object);
+/* Proof<Engine>::toJson().dump() (src/groth16.cpp:216-250, src/ultra_groth.cpp:476-513): proof points in the reference's
+ * G1PointAffine / G2PointAffine layout -> the JSON text the C API emits.  ultra == 0: A, B, C -> pi_a, pi_b, pi_c, "groth16";
+ * ultra != 0: A, B, C = final commitment, R = round commitment -> pi_a, pi_b, pi_f, pi_r, "ultragroth".  NUL terminated. */
+int ugb_proof_points_to_json(int ultra, const void* A64, const void* B128, const void* C64, const void* R64, char* out, uint64_t cap);
+
 /* ---- point-range sharded proving ("MSMs shard by point range across GPUs, partial sums reduced
  * on the host or via NCCL") ----
  * One prover object per GPU / process keeps slice `rank` of `world` of every zkey base array resident (A, B1, B2, C,

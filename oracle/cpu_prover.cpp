@@ -285,6 +285,39 @@ void h_scalars(const Zkey& zk, const Fr* w, std::vector<Fr>& a, int threads, dou
     if (t_ms) t_ms[1] += tm.lap() * 1e3;
 }
 
+// derive_challenge (src/ultra_groth.cpp:32-58): keccak256(BE32(x) || BE32(y)) of the canonical affine coordinates, digest read
+// big-endian into 4 limbs UNREDUCED, then one Montgomery multiplication by R^2 (RawFr::fromMpz, build/fr.cpp:286-290)
+Fr deriveChallenge(const Aff<Fq>& R) {
+    uint8_t buf[64], dig[32];
+    Fq x = fromMont(R.x), y = fromMont(R.y);
+    for (int i = 0; i < 32; i++) {
+        buf[i] = (uint8_t)(x.v[(31 - i) >> 3] >> (8 * ((31 - i) & 7)));
+        buf[32 + i] = (uint8_t)(y.v[(31 - i) >> 3] >> (8 * ((31 - i) & 7)));
+    }
+    keccak256(buf, 64, dig);
+    Fr raw = {{0, 0, 0, 0}};
+    for (int i = 0; i < 32; i++) raw.v[(31 - i) >> 3] |= (u64)dig[i] << (8 * ((31 - i) & 7));
+    return toMont(raw);
+}
+
+// compute_lookup (src/ultra_groth.cpp:62-106): w[wtns_idx[k]] = push[push_idx[k]], push = [rand | inv2[chunks[*]] | inv2 | prod]
+void computeLookup(Fr* w, const uint32_t* chunks, size_t K, const uint32_t* freqs, size_t T, const uint32_t* widx, const uint32_t* pidx, size_t NI,
+                   const Fr& rand, int threads) {
+    std::vector<Fr> push(1 + K + 2 * T);
+    push[0] = fromMont(rand);
+#pragma omp parallel for num_threads(threads)
+    for (size_t i = 0; i < T; i++) {
+        Fr iv = inv(add(fromU64<FrP>(i), rand));
+        push[1 + K + i] = fromMont(iv);
+        // uint32_t -> int conversion of the reference (build/fr.hpp:251, RawFr::set(int) build/fr.cpp:209-223): f >= 2^31 is negative
+        const int32_t fs = (int32_t)freqs[i];
+        Fr fm = fs < 0 ? neg(fromU64<FrP>((u64)(-(int64_t)fs))) : fromU64<FrP>((u64)fs);
+        push[1 + K + T + i] = fromMont(mul(fm, iv));
+    }
+    for (size_t j = 0; j < K; j++) push[1 + j] = push[1 + K + chunks[j]];
+    for (size_t k = 0; k < NI; k++) w[widx[k]] = push[pidx[k]];
+}
+
 struct ProofOut {
     Aff<Fq> A, C, R;
     Aff<Fq2> B;
@@ -349,36 +382,10 @@ int cpu_prove2(const uint8_t* zkey, u64 zkey_size, const uint8_t* wtns, u64 wtns
             if (out_msms) { Aff<Fq> t = toAff(commit); memcpy(out_msms + 384, &t, 64); }
             commit = addj(commit, mulScalar(affBytes<Fq>(zk.delta1), rk));
             out.R = toAff(commit);
-            // derive_challenge (:32-58)
-            uint8_t buf[64], dig[32];
-            Fq x = fromMont(out.R.x), y = fromMont(out.R.y);
-            for (int i = 0; i < 32; i++) {
-                buf[i] = (uint8_t)(x.v[(31 - i) >> 3] >> (8 * ((31 - i) & 7)));
-                buf[32 + i] = (uint8_t)(y.v[(31 - i) >> 3] >> (8 * ((31 - i) & 7)));
-            }
-            keccak256(buf, 64, dig);
-            Fr raw = {{0, 0, 0, 0}};
-            for (int i = 0; i < 32; i++) raw.v[(31 - i) >> 3] |= (u64)dig[i] << (8 * ((31 - i) & 7));
-            Fr rand = toMont(raw);
+            Fr rand = deriveChallenge(out.R);
             // compute_lookup (:62-106)
-            const uint32_t* chunks = (const uint32_t*)wf.data(3);
-            const uint32_t* freqs = (const uint32_t*)wf.data(4);
-            const uint32_t* widx = (const uint32_t*)wf.data(5);
-            const uint32_t* pidx = (const uint32_t*)wf.data(6);
-            size_t K = wf.size(3) / 4, T = wf.size(4) / 4, NI = wf.size(5) / 4;
-            std::vector<Fr> push(1 + K + 2 * T);
-            push[0] = fromMont(rand);
-#pragma omp parallel for num_threads(threads)
-            for (size_t i = 0; i < T; i++) {
-                Fr iv = inv(add(fromU64<FrP>(i), rand));
-                push[1 + K + i] = fromMont(iv);
-                // uint32_t -> int conversion of the reference (build/fr.hpp:251, RawFr::set(int) build/fr.cpp:209-223): f >= 2^31 is negative
-                const int32_t fs = (int32_t)freqs[i];
-                Fr fm = fs < 0 ? neg(fromU64<FrP>((u64)(-(int64_t)fs))) : fromU64<FrP>((u64)fs);
-                push[1 + K + T + i] = fromMont(mul(fm, iv));
-            }
-            for (size_t j = 0; j < K; j++) push[1 + j] = push[1 + K + chunks[j]];
-            for (size_t k = 0; k < NI; k++) w[widx[k]] = push[pidx[k]];
+            computeLookup(w.data(), (const uint32_t*)wf.data(3), wf.size(3) / 4, (const uint32_t*)wf.data(4), wf.size(4) / 4,
+                          (const uint32_t*)wf.data(5), (const uint32_t*)wf.data(6), wf.size(5) / 4, rand, threads);
             cw.resize(zk.nC2);
             for (uint32_t i = 0; i < zk.nC2; i++) cw[i] = w[rd32(zk.idx2 + 4 * (size_t)i)];
             nC = zk.nC2;
@@ -462,6 +469,19 @@ int cpu_field_mul(int field, const uint8_t* a, const uint8_t* b, uint8_t* out, u
     return 0;
 }
 void cpu_keccak256(const uint8_t* in, u64 len, uint8_t* out) { keccak256(in, len, out); }
+// the two UltraGroth host steps on their own (pinned against the reference's compiled RawFr / RawFq / keccak in tests/test_oracle.py)
+void cpu_derive_challenge(const uint8_t* commitment_xy_mont, uint8_t* rand_mont_out) {
+    Aff<Fq> R;
+    memcpy(&R, commitment_xy_mont, 64);
+    Fr r = deriveChallenge(R);
+    memcpy(rand_mont_out, &r, 32);
+}
+void cpu_compute_lookup(uint8_t* signals, const uint32_t* chunks, u64 K, const uint32_t* freqs, u64 T, const uint32_t* widx, const uint32_t* pidx,
+                        u64 NI, const uint8_t* rand_mont) {
+    Fr r;
+    memcpy(&r, rand_mont, 32);
+    computeLookup((Fr*)signals, chunks, K, freqs, T, widx, pidx, NI, r, 1);
+}
 int cpu_max_threads() { return omp_get_max_threads(); }
 
 }  // extern "C"

@@ -30,6 +30,10 @@ def lib():
         L.cpu_field_mul.argtypes = [i32, vp, vp, vp, u64]
         L.cpu_keccak256.argtypes = [vp, u64, vp]
         L.cpu_keccak256.restype = None
+        L.cpu_derive_challenge.argtypes = [vp, vp]
+        L.cpu_derive_challenge.restype = None
+        L.cpu_compute_lookup.argtypes = [vp, vp, u64, vp, u64, vp, vp, u64, vp]
+        L.cpu_compute_lookup.restype = None
         _lib = L
     return _lib
 
@@ -97,7 +101,7 @@ def msm(group, bases, scalars, n, threads=0):
 
 
 def ntt(data, logn, inverse=False, threads=0):
-    d = _arr(data)
+    d = _arr(data).copy()  # cpu_ntt works in place: never on the caller's array
     lib().cpu_ntt(_ptr(d), logn, 1 if inverse else 0, threads)
     return d.tobytes()
 
@@ -114,6 +118,22 @@ def keccak256(data: bytes) -> bytes:
     out = np.zeros(32, dtype=np.uint8)
     lib().cpu_keccak256(_ptr(d), len(data), _ptr(out))
     return out.tobytes()
+
+
+def derive_challenge(commitment_xy_mont: bytes) -> int:
+    a = _arr(commitment_xy_mont)
+    out = np.zeros(32, dtype=np.uint8)
+    lib().cpu_derive_challenge(_ptr(a), _ptr(out))
+    return int.from_bytes(out.tobytes(), "little")
+
+
+def compute_lookup(signals: bytes, chunks, freqs, wtns_idx, push_idx, rand_mont: int) -> bytes:
+    s = _arr(signals).copy()
+    u = lambda v: np.ascontiguousarray(np.asarray(v, dtype=np.uint32))
+    c, f, w, q = u(chunks), u(freqs), u(wtns_idx), u(push_idx)
+    r = _arr(int(rand_mont).to_bytes(32, "little"))
+    lib().cpu_compute_lookup(_ptr(s), _ptr(c), len(c), _ptr(f), len(f), _ptr(w), _ptr(q), len(w), _ptr(r))
+    return s.tobytes()
 
 
 def bench(workload, sample_logn, target_logn, threads=None):

@@ -1,7 +1,8 @@
-/* Minimal <gmp.h> stand-in (OURS, test infrastructure): prototypes of the mpn_* entry points that the
- * reference's generated field code (build/f{r,q}_raw_generic.cpp) calls, bound to the runtime
- * libgmp.so.10 of this image (the development header is not installed).  Functions GMP implements as
- * header macros / inlines are spelled out here. */
+/* Minimal <gmp.h> stand-in (OURS, test infrastructure): prototypes of the mpn_* / mpz_* entry points that the
+ * reference's generated field code (build/f{r,q}_raw_generic.cpp, build/f{r,q}.cpp, build/f{r,q}_generic.cpp) and its file
+ * loaders (src/zkey_utils.cpp, src/wtns_utils.cpp) call, bound to the runtime libgmp.so.10 of this image (the development
+ * header is not installed).  Functions GMP implements as header macros / inlines are spelled out here; __mpz_struct has
+ * GMP's documented layout. */
 #ifndef UGB_REF_SHIM_GMP_H
 #define UGB_REF_SHIM_GMP_H
 #include <stddef.h>
@@ -12,9 +13,41 @@ typedef long mp_size_t;
 typedef mp_limb_t* mp_ptr;
 typedef const mp_limb_t* mp_srcptr;
 
+typedef struct {
+    int _mp_alloc;
+    int _mp_size;
+    mp_limb_t* _mp_d;
+} __mpz_struct;
+typedef __mpz_struct mpz_t[1];
+typedef __mpz_struct* mpz_ptr;
+typedef const __mpz_struct* mpz_srcptr;
+
 #ifdef __cplusplus
 extern "C" {
 #endif
+void __gmpz_init(mpz_ptr);
+void __gmpz_clear(mpz_ptr);
+void __gmpz_import(mpz_ptr, size_t, int, size_t, int, size_t, const void*);
+void* __gmpz_export(void*, size_t*, int, size_t, int, size_t, mpz_srcptr);
+char* __gmpz_get_str(char*, int, mpz_srcptr);
+void __gmpz_fdiv_r(mpz_ptr, mpz_srcptr, mpz_srcptr);
+void __gmpz_fdiv_q(mpz_ptr, mpz_srcptr, mpz_srcptr);
+void __gmpz_add(mpz_ptr, mpz_srcptr, mpz_srcptr);
+void __gmpz_sub(mpz_ptr, mpz_srcptr, mpz_srcptr);
+void __gmpz_mul(mpz_ptr, mpz_srcptr, mpz_srcptr);
+void __gmpz_set(mpz_ptr, mpz_srcptr);
+void __gmpz_set_si(mpz_ptr, long);
+void __gmpz_set_ui(mpz_ptr, unsigned long);
+int __gmpz_invert(mpz_ptr, mpz_srcptr, mpz_srcptr);
+void __gmpz_init_set_ui(mpz_ptr, unsigned long);
+void __gmpz_init_set_si(mpz_ptr, long);
+int __gmpz_init_set_str(mpz_ptr, const char*, int);
+size_t __gmpz_sizeinbase(mpz_srcptr, int);
+void __gmpz_powm(mpz_ptr, mpz_srcptr, mpz_srcptr, mpz_srcptr);
+void __gmpz_mul_2exp(mpz_ptr, mpz_srcptr, unsigned long);
+long __gmpz_get_si(mpz_srcptr);
+int __gmpz_fits_sint_p(mpz_srcptr);
+int __gmpz_cmp(mpz_srcptr, mpz_srcptr);
 mp_limb_t __gmpn_add_n(mp_ptr, mp_srcptr, mp_srcptr, mp_size_t);
 mp_limb_t __gmpn_sub_n(mp_ptr, mp_srcptr, mp_srcptr, mp_size_t);
 mp_limb_t __gmpn_add_1(mp_ptr, mp_srcptr, mp_size_t, mp_limb_t);
@@ -31,6 +64,29 @@ void __gmpn_and_n(mp_ptr, mp_srcptr, mp_srcptr, mp_size_t);
 }
 #endif
 
+#define mpz_init __gmpz_init
+#define mpz_clear __gmpz_clear
+#define mpz_import __gmpz_import
+#define mpz_export __gmpz_export
+#define mpz_get_str __gmpz_get_str
+#define mpz_fdiv_r __gmpz_fdiv_r
+#define mpz_fdiv_q __gmpz_fdiv_q
+#define mpz_add __gmpz_add
+#define mpz_sub __gmpz_sub
+#define mpz_mul __gmpz_mul
+#define mpz_set __gmpz_set
+#define mpz_set_si __gmpz_set_si
+#define mpz_set_ui __gmpz_set_ui
+#define mpz_invert __gmpz_invert
+#define mpz_init_set_ui __gmpz_init_set_ui
+#define mpz_init_set_si __gmpz_init_set_si
+#define mpz_init_set_str __gmpz_init_set_str
+#define mpz_sizeinbase __gmpz_sizeinbase
+#define mpz_powm __gmpz_powm
+#define mpz_mul_2exp __gmpz_mul_2exp
+#define mpz_get_si __gmpz_get_si
+#define mpz_fits_sint_p __gmpz_fits_sint_p
+#define mpz_cmp __gmpz_cmp
 #define mpn_add_n __gmpn_add_n
 #define mpn_sub_n __gmpn_sub_n
 #define mpn_add_1 __gmpn_add_1

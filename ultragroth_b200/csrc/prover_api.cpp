@@ -814,6 +814,28 @@ int ugb_ultra_groth_prove_raw(void* prover_object, void* wtns_signals, const uin
     API_CATCH_PROVE
 }
 
+void ugb_prover_destroy(void* prover_object) {
+    if (prover_object != NULL) delete static_cast<ProverBase*>(prover_object);
+}
+
+int ugb_proof_points_to_json(int ultra, const void* A64, const void* B128, const void* C64, const void* R64, char* out, uint64_t cap) {
+    EXT_TRY
+    if (!A64 || !B128 || !C64 || !out || (ultra && !R64)) throw std::invalid_argument("Null argument");
+    HG1Affine A, C, R;
+    HG2Affine B;
+    memcpy(&A, A64, 64); memcpy(&B, B128, 128); memcpy(&C, C64, 64);
+    std::string js;
+    if (ultra) {
+        memcpy(&R, R64, 64);
+        js = "{\"pi_a\":" + g1_json(A) + ",\"pi_b\":" + g2_json(B) + ",\"pi_f\":" + g1_json(C) + ",\"pi_r\":" + g1_json(R) + ",\"protocol\":\"ultragroth\"}";
+    } else {
+        js = "{\"pi_a\":" + g1_json(A) + ",\"pi_b\":" + g2_json(B) + ",\"pi_c\":" + g1_json(C) + ",\"protocol\":\"groth16\"}";
+    }
+    if (js.size() + 1 > cap) throw std::length_error("proof JSON buffer too short");
+    memcpy(out, js.c_str(), js.size() + 1);
+    EXT_CATCH
+}
+
 // ---- point-range sharded proving (declared in include/ultragroth_b200.h) ---------
 // One prover object per GPU/process holds slice `rank` of `world` of every base array.  The MSM partial sums are
 // plain host structs (ugb_prover_partial_size() bytes) that the caller exchanges (NCCL / gloo all-gather, or a

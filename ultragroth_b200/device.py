@@ -19,7 +19,8 @@ class DeviceArray:
 
     def free(self):
         if self.ptr:
-            lib().ugb_free(self.ctx.handle, self.ptr)
+            if self.ctx.handle:  # the context may already be closed (arrays kept alive by a traceback): its memory went with it
+                lib().ugb_free(self.ctx.handle, self.ptr)
             self.ptr = None
 
     def __del__(self):
