@@ -35,6 +35,7 @@ typedef struct ugb_ctx ugb_ctx;
 #define UGB_OP_TO_MONT 4    /* Fr_rawToMontgomery   build/fr_raw_generic.cpp:150 */
 #define UGB_OP_FROM_MONT 5  /* Fr_rawFromMontgomery build/fr_raw_generic.cpp:155 */
 #define UGB_OP_SQR 6        /* Fr_rawMSquare     build/fr_raw_generic.cpp:150 */
+#define UGB_OP_MUL_DFMA 7   /* Fr_rawMMul through the FP64-assisted product (fp_mul_dfma, csrc/ff.cuh): same values */
 
 const char* ugb_last_error(void);
 int ugb_device_count(void);
@@ -178,7 +179,8 @@ int ugb_ultra_prove_assemble(void* prover_object, const void* partials, uint32_t
 /* ---- microbenchmarks for the roofline denominators ----
  * kind 0: independent 32-bit IMAD chains; 1: IMAD.WIDE (mad.wide.u32) chains; 2: dependent Fq Montgomery
  * products (4 chains per thread); 3 / 4: IMAD.WIDE rows with carry-in+out / carry-out only; 5: kind 2 on the Karatsuba product
- * fp_mul_ks.  Returns operations per second in *ops_per_s. */
+ * fp_mul_ks; 6: independent DFMA (fma.rz.f64) chains -- the FP64 pipe's peak; 7: kind 2 on the FP64-assisted product fp_mul_dfma.
+ * Returns operations per second in *ops_per_s. */
 int ugb_bench_int_pipe(ugb_ctx* ctx, int kind, double* ops_per_s);
 
 /* ---- harness tooling: synthetic circuits with a VALID trusted setup ----

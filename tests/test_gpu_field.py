@@ -48,6 +48,32 @@ def test_mul_unreduced_first_operand(ctx, field, mod):
     assert _run(ctx, field, 0, xs, ys) == [bn.mont_mul(x, y, mod) for x, y in zip(xs, ys)]
 
 
+@pytest.mark.parametrize("field,mod", [(0, bn.R), (1, bn.Q)])
+def test_fp64_assisted_product_bit_exact(ctx, field, mod):
+    """fp_mul_dfma (csrc/ff.cuh): x*y on the integer multiplier, the m*p half of the Montgomery reduction on the FP64 pipe (exact
+    52-bit limb products from round-towards-zero FMAs).  Same values as Fr_rawMMul for every input, including the rare case where
+    the dropped low columns borrow through bit 256 (inputs built so that x*y mod 2^256 = 2^256 - L with L small)."""
+    rng = random.Random(4321 + field)
+    edge = [0, 1, 2, mod - 1, mod - 2, (1 << 256) % mod, (1 << 255) % mod, mod >> 1, 0xffffffff, 1 << 32, (1 << 64) - 1, (1 << 224) - 1]
+    xs, ys = [], []
+    for e in edge:
+        for e2 in edge:
+            xs.append(e)
+            ys.append(e2)
+    for _ in range(60000):
+        xs.append(rng.randrange(mod))
+        ys.append(rng.randrange(mod))
+    for _ in range(20000):  # any 256-bit first operand
+        xs.append(rng.randrange(1 << 256))
+        ys.append(rng.randrange(mod))
+    for _ in range(20000):  # borrow-repair path: x = (2^256 - L) * y^-1 mod 2^256, L of every magnitude up to 2^222
+        y = rng.randrange(mod) | 1
+        L = rng.randrange(1, 1 << rng.randrange(1, 223))
+        xs.append(((1 << 256) - L) * pow(y, -1, 1 << 256) % (1 << 256))
+        ys.append(y)
+    assert _run(ctx, field, 7, xs, ys) == [bn.mont_mul(x, y, mod) for x, y in zip(xs, ys)]
+
+
 def test_empty_vector(ctx):
     a = ctx.upload(b"")
     ctx.field_vec_op(0, 0, a, a, a, 0)

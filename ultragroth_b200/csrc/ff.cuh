@@ -48,6 +48,7 @@ UG_D uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm vo
 UG_D uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
 UG_D uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.hi.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
 UG_D uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+UG_D uint32_t madc_lo(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
 #else
 // host emulation of the PTX condition-code register (tests only)
 static thread_local uint32_t g_cc = 0;
@@ -64,6 +65,32 @@ inline uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { return add_cc(a 
 inline uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { return addc_cc(a * b, c); }
 inline uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { return addc_cc(mul_hi(a, b), c); }
 inline uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) { return addc(mul_hi(a, b), c); }
+inline uint32_t madc_lo(uint32_t a, uint32_t b, uint32_t c) { return addc(a * b, c); }
+#endif
+
+// FP64 primitives of the hybrid product (fp_mul_dfma): fused multiply-add rounding TOWARDS ZERO and bit casts
+#if defined(__CUDA_ARCH__)
+UG_D double fma_rz(double a, double b, double c) { return __fma_rz(a, b, c); }
+UG_D double dsub(double a, double b) { return __dsub_rn(a, b); }
+UG_D double make_double(uint32_t hi, uint32_t lo) { return __hiloint2double((int)hi, (int)lo); }
+UG_D uint64_t double_bits(double d) { return (uint64_t)__double_as_longlong(d); }
+#else
+}  // namespace ug
+#include <cfenv>
+#include <cmath>
+#include <cstring>
+namespace ug {
+inline double fma_rz(double a, double b, double c) {  // tests only: the host FPU in round-towards-zero mode for one operation
+    const int old = fegetround();
+    fesetround(FE_TOWARDZERO);
+    volatile double va = a, vb = b, vc = c;
+    volatile double r = std::fma(va, vb, vc);
+    fesetround(old);
+    return r;
+}
+inline double dsub(double a, double b) { volatile double va = a, vb = b; return va - vb; }
+inline double make_double(uint32_t hi, uint32_t lo) { uint64_t u = ((uint64_t)hi << 32) | lo; double d; memcpy(&d, &u, 8); return d; }
+inline uint64_t double_bits(double d) { uint64_t u; memcpy(&u, &d, 8); return u; }
 #endif
 
 // ------------------------------------------------------------------------------------------------
@@ -71,6 +98,14 @@ inline uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) { return addc(mul_hi
 // ------------------------------------------------------------------------------------------------
 struct FrParams {
     static constexpr uint32_t NP0 = 0xefffffffu;  // low word of Fr_np = 0xc2e1f593efffffff
+    UG_HD static constexpr uint32_t np(int i) {  // -r^-1 mod 2^256
+        constexpr uint32_t m[8] = {0xefffffffu, 0xc2e1f593u, 0x4c6911b3u, 0x6586864bu, 0x99062391u, 0xe39a9828u, 0x0d8341b2u, 0x73f82f1du};
+        return m[i];
+    }
+    UG_HD static constexpr double mod16_52(int i) {  // 16*r in 52-bit limbs (exact integers as doubles)
+        constexpr double m[5] = {4320251768471568.0, 2385637178164193.0, 2275464320335492.0, 45871597467265.0, 851317936231194.0};
+        return m[i];
+    }
     UG_HD static constexpr uint32_t mod(int i) {
         constexpr uint32_t m[8] = {0xf0000001u, 0x43e1f593u, 0x79b97091u, 0x2833e848u,
                                    0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
@@ -90,6 +125,14 @@ struct FrParams {
 
 struct FqParams {
     static constexpr uint32_t NP0 = 0xe4866389u;  // low word of Fq_np = 0x87d20782e4866389
+    UG_HD static constexpr uint32_t np(int i) {  // -q^-1 mod 2^256
+        constexpr uint32_t m[8] = {0xe4866389u, 0x87d20782u, 0x1eca6ac9u, 0x9ede7d65u, 0x1833da80u, 0xd8afcbd0u, 0x91888c6bu, 0xf57a22b7u};
+        return m[i];
+    }
+    UG_HD static constexpr double mod16_52(int i) {  // 16*q in 52-bit limbs (exact integers as doubles)
+        constexpr double m[5] = {2464475987825776.0, 396312915557408.0, 2275464437044905.0, 45871597467265.0, 851317936231194.0};
+        return m[i];
+    }
     UG_HD static constexpr uint32_t mod(int i) {
         constexpr uint32_t m[8] = {0xd87cfd47u, 0x3c208c16u, 0x6871ca8du, 0x97816a91u,
                                    0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
@@ -396,6 +439,179 @@ UG_HD Fp<P> fp_mul_ks(const Fp<P>& x, const Fp<P>& y) {
 #pragma unroll
     for (int k = 1; k < 7; k++) r.v[k] = addc_cc(e[k], o[k + 1]);
     r.v[7] = addc(e[7], T[15]);
+    fp_final_sub(r);
+    return r;
+}
+
+// ---- FP64-assisted Montgomery product (sm_100a: B200 has a full-rate FP64 pipe that every kernel here leaves idle) -----------
+// fp_mul spends 64 of its 136 wide multiply-adds on m*p, a product by a CONSTANT.  Here that half moves to the FP64 pipe:
+//   T  = x*y                      16 limbs, 64 IMAD.WIDE (product scanning, even / odd accumulators)
+//   m  = T_lo * (-p^-1) mod 2^256 low half product, 28 IMAD.WIDE + 8 IMAD
+//   h  = floor(m*p / 2^256)       on the FP64 pipe: m and 16*p in five 52-bit limbs held as doubles; every limb product
+//                                 a*b = H*2^52 + L is split EXACTLY by two round-towards-zero FMAs
+//                                     hi = fma_rz(a, b, 2^104)               = 2^104 + H*2^52     (the mantissa IS H)
+//                                     lo = fma_rz(a, b, (2^104 + 2^52) - hi) = 2^52 + L           (the mantissa IS L)
+//                                 and the raw bit patterns are summed per 52-bit column as 64-bit integers.  Only the columns
+//                                 that reach bit 260 of m*16p are formed: 15 full products (i+j >= 4) and 4 high halves (i+j = 3);
+//                                 what is dropped is < 2^216 and is accounted for exactly, because the low 256 bits of m*p are
+//                                 KNOWN: they are -T_lo mod 2^256 (that is what m is chosen for)
+//   r  = T_hi + h + (T_lo != 0), one conditional subtraction -- the same value as fp_mul(x, y) for x, y < p.
+// Per product: 92 IMAD.WIDE + 8 IMAD instead of 136 IMAD.WIDE on the multiplier pipe, 54 operations on the FP64 pipe, the rest ALU.
+
+// T[0..15] = a[0..7] * b[0..7]
+UG_HD void mul8x8(const uint32_t* a, const uint32_t* b, uint32_t* T) {
+    uint32_t ev[16], od[16];  // od[k] sits at limb k+1
+#pragma unroll
+    for (int k = 0; k < 16; k++) { ev[k] = 0; od[k] = 0; }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const uint32_t x = b[i];
+        // limb pairs starting at an even position go to ev, at an odd position to od: every (lo, hi) pair is one aligned IMAD.WIDE
+        uint32_t* A0 = (i & 1) ? od : ev;  // receives a[even k] * x at position i + k
+        uint32_t* A1 = (i & 1) ? ev : od;  // receives a[odd k]  * x at position i + k
+        const int o0 = (i & 1) ? i - 1 : i;      // index inside A0 of position i      (od index = position - 1)
+        const int o1 = (i & 1) ? i + 1 : i;      // index inside A1 of position i + 1
+        A0[o0 + 0] = mad_lo_cc(a[0], x, A0[o0 + 0]);
+        A0[o0 + 1] = madc_hi_cc(a[0], x, A0[o0 + 1]);
+        A0[o0 + 2] = madc_lo_cc(a[2], x, A0[o0 + 2]);
+        A0[o0 + 3] = madc_hi_cc(a[2], x, A0[o0 + 3]);
+        A0[o0 + 4] = madc_lo_cc(a[4], x, A0[o0 + 4]);
+        A0[o0 + 5] = madc_hi_cc(a[4], x, A0[o0 + 5]);
+        A0[o0 + 6] = madc_lo_cc(a[6], x, A0[o0 + 6]);
+        A0[o0 + 7] = madc_hi_cc(a[6], x, A0[o0 + 7]);
+        if (o0 + 8 < 16) A0[o0 + 8] = addc(A0[o0 + 8], 0);
+        A1[o1 + 0] = mad_lo_cc(a[1], x, A1[o1 + 0]);
+        A1[o1 + 1] = madc_hi_cc(a[1], x, A1[o1 + 1]);
+        A1[o1 + 2] = madc_lo_cc(a[3], x, A1[o1 + 2]);
+        A1[o1 + 3] = madc_hi_cc(a[3], x, A1[o1 + 3]);
+        A1[o1 + 4] = madc_lo_cc(a[5], x, A1[o1 + 4]);
+        A1[o1 + 5] = madc_hi_cc(a[5], x, A1[o1 + 5]);
+        A1[o1 + 6] = madc_lo_cc(a[7], x, A1[o1 + 6]);
+        A1[o1 + 7] = madc_hi_cc(a[7], x, A1[o1 + 7]);
+        if (o1 + 8 < 16) A1[o1 + 8] = addc(A1[o1 + 8], 0);
+    }
+    T[0] = ev[0];
+    T[1] = add_cc(ev[1], od[0]);
+#pragma unroll
+    for (int k = 2; k < 15; k++) T[k] = addc_cc(ev[k], od[k - 1]);
+    T[15] = addc(ev[15], od[14]);
+}
+
+// m[0..7] = low 256 bits of t[0..7] * P::np[0..7] (compile-time constants): 28 wide products and 8 low words
+template <class P>
+UG_HD void mullo8x8_np(const uint32_t* t, uint32_t* m) {
+    uint32_t ev[8], od[8];  // od[k] sits at limb k+1; limbs >= 8 are never formed
+#pragma unroll
+    for (int k = 0; k < 8; k++) { ev[k] = 0; od[k] = 0; }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const uint32_t x = t[i];
+        // row i: products np[k] * x at limb position i + k for k <= 7 - i.  Two carry chains per row, one over the even k and one over
+        // the odd k; each runs over CONSECUTIVE limbs up to limb 7 of its accumulator (even positions -> ev, odd -> od), so the
+        // carry of every pair is consumed by the next pair and the one past limb 7 is dropped (arithmetic mod 2^256).
+#pragma unroll
+        for (int k0 = 0; k0 < 2; k0++) {
+            if (i + k0 > 7) continue;
+            const bool even = ((i + k0) & 1) == 0;
+            uint32_t* A = even ? ev : od;
+            bool carry = false;
+#pragma unroll
+            for (int k = k0; i + k < 8; k += 2) {
+                const int pos = i + k;
+                const int o = even ? pos : pos - 1;
+                if (pos == 7) {  // only the low word of this product is below 2^256 (pos 7 is odd: od[6])
+                    A[o] = carry ? madc_lo(P::np(k), x, A[o]) : A[o] + mul_lo(P::np(k), x);
+                } else {
+                    A[o] = carry ? madc_lo_cc(P::np(k), x, A[o]) : mad_lo_cc(P::np(k), x, A[o]);
+                    // the high word ends the chain when the next pair would start at limb 8 or beyond
+                    if (pos + 2 < 8) A[o + 1] = madc_hi_cc(P::np(k), x, A[o + 1]);
+                    else A[o + 1] = madc_hi(P::np(k), x, A[o + 1]);
+                    carry = true;
+                }
+            }
+        }
+    }
+    m[0] = ev[0];
+    m[1] = add_cc(ev[1], od[0]);
+#pragma unroll
+    for (int k = 2; k < 7; k++) m[k] = addc_cc(ev[k], od[k - 1]);
+    m[7] = addc(ev[7], od[6]);
+}
+
+template <class P>
+UG_HD Fp<P> fp_mul_dfma(const Fp<P>& x, const Fp<P>& y) {
+    uint32_t T[16];
+    mul8x8(x.v, y.v, T);
+    uint32_t m[8];
+    mullo8x8_np<P>(T, m);
+    // m in five 52-bit limbs as doubles: (2^52 + limb) assembled from bits, then - 2^52 (exact)
+    const double two52 = 4503599627370496.0;
+    double md[5];
+    md[0] = dsub(make_double(0x43300000u | (m[1] & 0xfffffu), m[0]), two52);
+    md[1] = dsub(make_double(0x43300000u | (((m[3] << 12) | (m[2] >> 20)) & 0xfffffu), (m[2] << 12) | (m[1] >> 20)), two52);
+    md[2] = dsub(make_double(0x43300000u | ((m[4] >> 8) & 0xfffffu), (m[4] << 24) | (m[3] >> 8)), two52);
+    md[3] = dsub(make_double(0x43300000u | (((m[6] << 4) | (m[5] >> 28)) & 0xfffffu), (m[5] << 4) | (m[4] >> 28)), two52);
+    md[4] = dsub(make_double(0x43300000u | (m[7] >> 16), (m[7] << 16) | (m[6] >> 16)), two52);
+    // column sums of raw bit patterns: C[k] collects position 52*k of m * 16p, k = 4..9
+    const double c_hi = 20282409603651670423947251286016.0;            // 2^104
+    const double c_lo = 20282409603651670423947251286016.0 + two52;    // 2^104 + 2^52
+    const uint64_t bits_hi = 0x4670000000000000ull;                    // bit pattern of 2^104
+    const uint64_t bits_lo = 0x4330000000000000ull;                    // bit pattern of 2^52
+    uint64_t C[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+#pragma unroll
+        for (int j = 0; j < 5; j++) {
+            if (i + j < 3) continue;
+            const double hi = fma_rz(md[i], P::mod16_52(j), c_hi);
+            C[i + j + 1 - 4] += double_bits(hi);
+            if (i + j >= 4) {
+                const double lo = fma_rz(md[i], P::mod16_52(j), dsub(c_lo, hi));
+                C[i + j - 4] += double_bits(lo);
+            }
+        }
+    }
+    // strip the constants: column k-4 received n_hi(k) high halves (products with i+j = k-1) and n_lo(k) low halves (i+j = k)
+    C[0] -= 4 * bits_hi + 5 * bits_lo;  // k = 4
+    C[1] -= 5 * bits_hi + 4 * bits_lo;
+    C[2] -= 4 * bits_hi + 3 * bits_lo;
+    C[3] -= 3 * bits_hi + 2 * bits_lo;
+    C[4] -= 2 * bits_hi + 1 * bits_lo;
+    C[5] -= 1 * bits_hi;
+    // S = sum C[k] 2^(52 (k+4)) = m*16p - D with 0 <= D < 2^216.  m*16p = h*2^260 + 16*L, L = -T_lo mod 2^256 known.  floor(S / 2^260) is
+    // h, or h - 1 when the dropped part borrowed through bit 260, which shows as: bit 259 of S set while bit 255 of L is clear.
+    const uint64_t mask52 = 0xfffffffffffffull;
+    uint32_t tl_nz = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) tl_nz |= T[k];
+    // bit 255 of L = -T_lo mod 2^256: L = 2^256 - T_lo for T_lo != 0
+    uint32_t low7 = 0;
+#pragma unroll
+    for (int k = 0; k < 7; k++) low7 |= T[k];
+    const uint32_t neg_top = (low7 ? ~T[7] : 0u - T[7]);  // top limb of -T_lo mod 2^256
+    const uint32_t L_top_bit = tl_nz ? (neg_top >> 31) : 0u;
+    const uint32_t S_top_bit = (uint32_t)(C[0] >> 51) & 1u;
+    const uint64_t fix = (uint64_t)(S_top_bit & (L_top_bit ^ 1u)) + (tl_nz ? 1u : 0u);  // borrow repair + the carry of T_lo + (m*p)_lo
+    uint64_t c = (C[0] >> 52) + C[1] + fix;
+    uint64_t w0 = c & mask52; c = (c >> 52) + C[2];
+    uint64_t w1 = c & mask52; c = (c >> 52) + C[3];
+    uint64_t w2 = c & mask52; c = (c >> 52) + C[4];
+    uint64_t w3 = c & mask52; c = (c >> 52) + C[5];
+    uint64_t w4 = c;
+    uint32_t h[8];
+    h[0] = (uint32_t)w0;
+    h[1] = (uint32_t)(w0 >> 32) | (uint32_t)(w1 << 20);
+    h[2] = (uint32_t)(w1 >> 12);
+    h[3] = (uint32_t)(w1 >> 44) | (uint32_t)(w2 << 8);
+    h[4] = (uint32_t)(w2 >> 24) | (uint32_t)(w3 << 28);
+    h[5] = (uint32_t)(w3 >> 4);
+    h[6] = (uint32_t)(w3 >> 36) | (uint32_t)(w4 << 16);
+    h[7] = (uint32_t)(w4 >> 16);
+    Fp<P> r;
+    r.v[0] = add_cc(T[8], h[0]);
+#pragma unroll
+    for (int k = 1; k < 7; k++) r.v[k] = addc_cc(T[8 + k], h[k]);
+    r.v[7] = addc(T[15], h[7]);
     fp_final_sub(r);
     return r;
 }

@@ -17,7 +17,8 @@ __global__ void __launch_bounds__(256) k_field_vec(const F* __restrict__ a, cons
         else if (OP == 3) r = fp_neg(x);
         else if (OP == 4) r = fp_to_mont(x);
         else if (OP == 5) r = fp_from_mont(x);
-        else r = fp_sqr(x);
+        else if (OP == 6) r = fp_sqr(x);
+        else r = fp_mul_dfma(x, ld_g(&b[i]));
         st_g(&out[i], r);
     }
 }
@@ -36,6 +37,7 @@ static void launch_vec(DeviceCtx& ctx, int op, const void* a, const void* b, voi
         case 4: k_field_vec<F, 4><<<blocks, 256, 0, ctx.stream>>>(A, Bp, O, n); break;
         case 5: k_field_vec<F, 5><<<blocks, 256, 0, ctx.stream>>>(A, Bp, O, n); break;
         case 6: k_field_vec<F, 6><<<blocks, 256, 0, ctx.stream>>>(A, Bp, O, n); break;
+        case 7: k_field_vec<F, 7><<<blocks, 256, 0, ctx.stream>>>(A, Bp, O, n); break;
         default: throw std::runtime_error("ultragroth_b200: unknown field op");
     }
     UG_LAUNCH_CHECK(ctx);

@@ -131,6 +131,38 @@ __global__ void __launch_bounds__(256) k_bench_modmul_ks(Fq* out, uint32_t seed)
     if (s.v[0] == 0x12345678u && s.v[7] == 1) out[0] = s;
 }
 
+// kind 6: the FP64 pipe's own peak: 8 independent fma.rz.f64 chains per thread
+__global__ void __launch_bounds__(256) k_bench_dfma(double* out, uint32_t seed) {
+    double a[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = 1.0 + 1e-9 * (double)(seed + threadIdx.x * 8 + i);
+    const double m = 1.0 + 1e-12 * (double)seed;
+    for (int it = 0; it < IB_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) a[i] = __fma_rz(a[i], m, a[(i + 1) & 7] * 1e-300);
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += a[i];
+    if (s == 0.12345) out[0] = s;
+}
+
+// kind 7: kind 2's dependent chains on the FP64-assisted product (fp_mul_dfma, ff.cuh)
+__global__ void __launch_bounds__(256) k_bench_modmul_dfma(Fq* out, uint32_t seed) {
+    Fq a[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        a[i] = Fq::one();
+        a[i].v[0] += seed + threadIdx.x + i;
+    }
+    for (int it = 0; it < MB_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) a[i] = fp_mul_dfma(a[i], a[(i + 1) & 3]);
+    }
+    Fq s = fp_add(fp_add(a[0], a[1]), fp_add(a[2], a[3]));
+    if (s.v[0] == 0x12345678u && s.v[7] == 1) out[0] = s;
+}
+
 double bench_int_pipe(DeviceCtx& ctx, int kind) {
     ctx.activate();
     void* d = ctx.workspace("intbench", 256);
@@ -146,6 +178,8 @@ double bench_int_pipe(DeviceCtx& ctx, int kind) {
         else if (kind == 1) { k_bench_imad_wide<<<blocks, 256, 0, ctx.stream>>>((uint64_t*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
         else if (kind == 3) { k_bench_imad_wide_x<<<blocks, 256, 0, ctx.stream>>>((uint32_t*)d, 7 + rep); ops = (double)blocks * 256 * 16 * (IB_ITERS / 2); }
         else if (kind == 4) { k_bench_imad_wide_cout<<<blocks, 256, 0, ctx.stream>>>((uint32_t*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
+        else if (kind == 6) { k_bench_dfma<<<blocks, 256, 0, ctx.stream>>>((double*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
+        else if (kind == 7) { k_bench_modmul_dfma<<<blocks, 256, 0, ctx.stream>>>((Fq*)d, 7 + rep); ops = (double)blocks * 256 * 4 * MB_ITERS; }
         else if (kind == 5) { k_bench_modmul_ks<<<blocks, 256, 0, ctx.stream>>>((Fq*)d, 7 + rep); ops = (double)blocks * 256 * 4 * MB_ITERS; }
         else { k_bench_modmul<<<blocks, 256, 0, ctx.stream>>>((Fq*)d, 7 + rep); ops = (double)blocks * 256 * 4 * MB_ITERS; }
         UG_LAUNCH_CHECK(ctx);
