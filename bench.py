@@ -31,6 +31,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-verify", action="store_true")
+    ap.add_argument("--no-shard", action="store_true", help="skip the sharded single-proof leg that --gpus N > 1 adds to the line")
     ap.add_argument("--shard", action="store_true",
                     help="one proof at a time over ALL ranks: MSMs sharded by point range (SURVEY 8(e)) instead of replicas")
     return ap.parse_args()
@@ -213,9 +214,7 @@ def main():
     t_create = time.time() - t_create
     zkey_bytes = int(zkey.nbytes)
     create_ms = prover.create_times()
-    keep_zkey = rank == 0 and world == 1 and not args.no_cpu  # the CPU baseline proves the very same files
-    if not keep_zkey:
-        del zkey
+    # kept on the host: the CPU baseline proves the very same files (N = 1), the sharded provers are created from them (N > 1)
 
     # pinned host witness: what the C API is handed every step
     wt = torch.from_numpy(wtns).pin_memory()
@@ -291,6 +290,11 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t_dev, t_e2e = float(t[0]), float(t[1])
 
+    # ---- the north star's multi-GPU split, measured in the same run: ONE proof at a time over all N ranks ----
+    shard_rec = None
+    if world > 1 and not args.no_shard:
+        shard_rec = sharded_leg(args, torch, dist, world, rank, local, zkey, wt_np, vkj, ultra, barrier)
+
     if rank == 0:
         n = 1 << args.logn
         peaks = {}
@@ -328,6 +332,7 @@ def main():
             "int_pipe_peak": {"imad_per_s": imad, "imad_wide_per_s": imad_wide, "imad_wide_kinds": wide_kinds, "fq_modmul_per_s": modmul},
             "wall_ms_per_step": 1000.0 * t_wall / args.steps,
             "setup_s": round(t_setup, 2), "create_s": round(t_create, 2), "create_ms": {k: round(v, 1) for k, v in create_ms.items()},
+            "inf_points": prover.inf_points(),
         }
         # second half of BASELINE.json's metric: G1 MSM points/s, taken from the proof's own H MSM (domainSize dense full-width
         # scalars against the resident table, sort + accumulate + reduce) and the A MSM (nVars witness scalars); whole job = x world
@@ -338,6 +343,8 @@ def main():
                 "note": "per-proof MSMs over resident window tables (c=22); standalone ad-hoc-base sweep: profiles/r01_sweep_g1.jsonl"}
         line["prove_latency_ms"] = {"resident": 1000.0 * t_dev / args.steps, "e2e": 1000.0 * t_e2e / args.steps}
         line["roofline"], line["roofline_ntt"] = rooflines(stats, args, nvars, n, hbm_peak, peak_src, imad_wide, ultra, chunks, lookup_bits)
+        if shard_rec is not None:
+            line["sharded"] = shard_rec
         if not args.no_cpu and world == 1:
             try:
                 line["cpu_baseline"] = cpu_prove_timed(args, zkey, wtns, 1, 0.0)
@@ -347,6 +354,56 @@ def main():
     prover.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def sharded_leg(args, torch, dist, world, rank, local, zkey, wt_np, vkj, ultra, barrier):
+    """Single-proof latency with everything sharded over the N ranks (ultragroth_b200/sharded.py prove2): every rank keeps 1/N of each
+    base table, uploads 1/N of the witness (all-gathered over NVLink), the a / b / c transforms run on three ranks and each rank gets
+    its range of a', b', c' for its share of the H MSM; the 896-byte partial sums are gathered and rank 0 assembles.  Also the
+    metric's "G1 MSM points/s at N GPUs": the sharded H MSM (domainSize dense scalars: digit sort + accumulate + reduce per rank)."""
+    from ultragroth_b200 import sharded
+    from ultragroth_b200 import verifier as uv
+    t0 = time.time()
+    sp = sharded.ShardedProver(zkey, "ultragroth" if ultra else "groth16", rank=rank, world=world)
+    t_create = time.time() - t0
+    comm = sharded.DistComm(sp)
+    rk = (1 << 200) + 0xB200  # common r_k for UltraGroth (any value < 2^248; fixed so that every rank agrees)
+    res = None
+    for _ in range(max(args.warmup, 3)):
+        res = sp.prove2(wt_np, rk=rk if ultra else None, comm=comm)
+    ok = None
+    if rank == 0 and not args.no_verify:
+        ok = bool(uv.verify("ultragroth" if ultra else "groth16", res[0], res[1], vkj))
+        if not ok:
+            raise SystemExit("bench: the sharded proof does not verify -- refusing to report a number")
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sp.prove2(wt_np, rk=rk if ultra else None, comm=comm)
+    barrier()
+    t = time.perf_counter() - t0
+    # G1 MSM points/s: the H MSM phase alone, timed with CUDA events on the prover's stream (h already in HBM from the last proof)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    barrier()
+    with comm.stream_scope():
+        ev0.record()
+        for _ in range(reps):
+            sp.h_msm()
+        ev1.record()
+    ev1.synchronize()
+    t_h = ev0.elapsed_time(ev1) * 1e-3 / reps
+    tt = torch.tensor([t, t_h], dtype=torch.float64, device="cuda")
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t, t_h = float(tt[0]), float(tt[1])
+    n = 1 << args.logn
+    rec = {"scaling": "strong", "ms_per_proof": 1000.0 * t / args.steps, "proofs_per_s": args.steps / t, "verified": ok,
+           "parallelism": f"bases, witness upload, H pipeline and MSMs sharded x{world}; one proof at a time",
+           "g1_msm_h": {"points": n, "ms": 1000.0 * t_h, "points_per_s": n / t_h,
+                        "what": "H MSM of the proof sharded by point range: k_h_final + digit sort + bucket accumulation + reduction per rank, max over ranks"},
+           "create_s": round(t_create, 2)}
+    sp.close()
+    return rec
 
 
 def main_sharded(args, torch, dist, world, rank, local):
@@ -376,9 +433,10 @@ def main_sharded(args, torch, dist, world, rank, local):
             dist.barrier()
         torch.cuda.synchronize()
 
+    comm = sharded.DistComm(sp)
     res = None
     for _ in range(max(args.warmup, 3)):
-        res = sp.prove(wt, rk=rk if ultra else None)
+        res = sp.prove2(wt, rk=rk if ultra else None, comm=comm)
     verified = None
     if rank == 0 and not args.no_verify:
         proof = og.proof_from_json(res[0])
@@ -394,7 +452,7 @@ def main_sharded(args, torch, dist, world, rank, local):
     t0 = time.perf_counter()
     ev0.record()
     for _ in range(args.steps):
-        sp.prove(wt, rk=rk if ultra else None)
+        sp.prove2(wt, rk=rk if ultra else None, comm=comm)
     ev1.record()
     barrier()
     t = max(time.perf_counter() - t0, ev0.elapsed_time(ev1) * 1e-3)
@@ -410,7 +468,7 @@ def main_sharded(args, torch, dist, world, rank, local):
                 "warmup": max(args.warmup, 3), "ms_per_step": 1000.0 * t / args.steps, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "u256 (8x32-bit Montgomery limbs, BN254 Fr/Fq)", "data": "synthetic",
                 "config": {"workload": workload_name(args), "nVars": nvars, "domainSize": 1 << args.logn,
-                           "parallelism": f"msm point-range shard x{world} (H pipeline replicated)",
+                           "parallelism": f"bases, witness upload, H pipeline and MSMs sharded x{world}",
                            "l2": "inputs exceed L2 (zkey bases %.2f GB over %d GPUs)" % (zkey_bytes / 1e9, world)},
                 "e2e": {"value": args.steps / t, "unit": "proofs/s", "ms_per_proof": 1000.0 * t / args.steps,
                         "h2d_bytes_per_step": int(wtns.nbytes), "d2h_bytes_per_step": int(sp.partial_size),

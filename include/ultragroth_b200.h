@@ -100,6 +100,8 @@ int ugb_prover_last_msms(void* prover_object, void* out448);
 int ugb_prover_last_witness(void* prover_object, void* out, uint64_t first, uint64_t count);
 /* create-time breakdown in ms: base uploads, coefficient CSR build (host threads, overlapped), window tables, total */
 int ugb_prover_create_times(void* prover_object, double* out4);
+/* zero-point maps found at create: points at infinity among pointsA, among pointsB1 AND pointsB2, among the (padded) pointsC */
+int ugb_prover_inf_points(void* prover_object, uint64_t* out3);
 /* per-stage CUDA-event times (ms) of the last proof: upload, round, lookup, sort_w, msm_a, msm_b1, msm_b2,
  * msm_c, spmv, intt, ntt, hfinal, sort_h, msm_h, total */
 int ugb_prover_set_timing(void* prover_object, int enable);
@@ -143,6 +145,34 @@ int ugb_ultra_groth_prove_raw(void* prover_object, void* wtns_signals, const uin
                               uint32_t frequencies_len, const uint32_t* wtns_indxs, const uint32_t* push_indxs, uint32_t wtns_indxs_len,
                               void* out_A64, void* out_B128, void* out_final_commitment64, void* out_round_commitment64, char* error_msg,
                               unsigned long long error_msg_maxsize);
+
+/* ---- sharded proving, phase by phase (what ultragroth_b200/sharded.py drives; SURVEY.md 8(e) both bullets) ----
+ * Nothing is replicated that does not have to be: every rank uploads only ITS slice of the witness over PCIe and the slices are
+ * all-gathered between the GPUs (NVLink) in place; the three transforms of the H pipeline (src/groth16.cpp:110-140) run on up to
+ * three different ranks and every rank receives just its point range of a', b', c' for the pointwise step and its share of the H MSM.
+ * The exchanges themselves (all-gather of w, slices of a/b/c, the 896-byte partial sums) are the CALLER's: the layout call hands out the
+ * device buffers; chunks are equal-sized (ceil(n / world), buffers padded) so that they map 1:1 onto collectives.  Order per proof:
+ *   upload_slice -> [all-gather w] -> (UltraGroth: round_partial -> [gather] -> lookup) -> h_transform(mask) -> [send slices of a,b,c]
+ *   -> witness_msms -> [recv] -> h_msm -> finish -> [gather partials] -> ugb_groth16_prove_assemble / ugb_ultra_prove_assemble.
+ * Return codes as include/prover.h. */
+typedef struct ugb_shard_layout {
+    void *w, *a, *b, *c;             /* device buffers: witness (world * w_chunk signals), a / b / c (world * h_chunk elements), 32 B each */
+    uint64_t nVars, domainSize;
+    uint64_t w_chunk, h_chunk;       /* rank r owns signals [r * w_chunk, min(nVars, (r+1) * w_chunk)) and H points likewise */
+    uint32_t rank, world;
+    int device;
+    void* stream;                    /* cudaStream_t every phase is enqueued on */
+} ugb_shard_layout;
+int ugb_shard_layout_get(void* prover_object, ugb_shard_layout* out);
+int ugb_shard_upload_slice(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, char* error_msg,
+                           unsigned long long error_msg_maxsize);
+int ugb_shard_round_partial(void* prover_object, void* round_partial_out128, char* error_msg, unsigned long long error_msg_maxsize);
+int ugb_shard_lookup(void* prover_object, const void* round_partials, uint32_t count, const void* rk32, char* error_msg,
+                     unsigned long long error_msg_maxsize);
+int ugb_shard_h_transform(void* prover_object, int vector_mask, char* error_msg, unsigned long long error_msg_maxsize);
+int ugb_shard_witness_msms(void* prover_object, char* error_msg, unsigned long long error_msg_maxsize);
+int ugb_shard_h_msm(void* prover_object, char* error_msg, unsigned long long error_msg_maxsize);
+int ugb_shard_finish(void* prover_object, void* partial_out, char* error_msg, unsigned long long error_msg_maxsize);
 
 /* destroys a prover made by ugb_prover_create_from_sections (same as groth16_prover_destroy / ultra_groth_prover_destroy) */
 void ugb_prover_destroy(void* prover_object);

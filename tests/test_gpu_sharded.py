@@ -75,6 +75,30 @@ def test_ultragroth_sharded_equals_unsharded(ctx, world):
     assert og.ultragroth_verify(og.vk_from_ultragroth_json(vkj), proof, public)
 
 
+@pytest.mark.parametrize("protocol,world", [("groth16", 2), ("groth16", 3), ("groth16", 5), ("ultragroth", 2), ("ultragroth", 4)])
+def test_phasewise_protocol_equals_unsharded(ctx, protocol, world):
+    """The de-replicated protocol (ugb_shard_*): witness SLICES uploaded and all-gathered, the a / b / c transforms on different
+    shards, every shard forming only its range of h -- byte-identical proofs to the unsharded prover (shards in one process, the
+    exchanges as device-to-device copies: sharded.prove_local)."""
+    ultra = protocol == "ultragroth"
+    if ultra:
+        zk, wt, vkj = ctx.synth(10, seed=779, ultra=True, lookup_bits=4, n_chunks=256)
+    else:
+        zk, wt, vkj = ctx.synth(10, seed=4243)
+    zk, wt = zk.tobytes(), wt.tobytes()
+    p = up.Prover(zk, protocol)
+    p.set_blinding(R_FIX, S_FIX, RK_FIX)
+    want = p.prove(wt)
+    p.close()
+    shards = [sharded.ShardedProver(zk, protocol, rank=r, world=world, exchange=lambda b: [b], root=None) for r in range(world)]
+    for s in shards:
+        s.set_blinding(R_FIX, S_FIX, RK_FIX)
+    out = sharded.prove_local(shards, wt, rk=RK_FIX if ultra else None)
+    for s in shards:
+        s.close()
+    assert out[0] == out[1] == want
+
+
 def _free_port():
     import socket
     with socket.socket() as so:

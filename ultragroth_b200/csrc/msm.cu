@@ -67,8 +67,22 @@ static void exclusive_scan_u32(DeviceCtx& ctx, const uint32_t* in, uint32_t n, u
     UG_KERNEL(ctx, "k_scan_apply", k_scan_apply<<<ntiles, SCAN_BS, 0, ctx.stream>>>(in, n, tiles, out));
 }
 
+uint64_t msm_inf_bitmap(DeviceCtx& ctx, int group, const void* d_bases, uint64_t n, uint32_t* d_bitmap, bool combine) {
+    ctx.activate();
+    if (n == 0) return 0;
+    uint32_t* d_count = (uint32_t*)ctx.workspace("msm.inf_count", 16);
+    UG_CUDA_CHECK(cudaMemsetAsync(d_count, 0, 4, ctx.stream));
+    const int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx.sm_count * 8);
+    if (group == 1) UG_KERNEL(ctx, "k_inf_bitmap", k_inf_bitmap<Fq><<<blocks, 256, 0, ctx.stream>>>((const G1Affine*)d_bases, (uint32_t)n, d_bitmap, combine ? 1 : 0, d_count));
+    else UG_KERNEL(ctx, "k_inf_bitmap", k_inf_bitmap<Fq2c><<<blocks, 256, 0, ctx.stream>>>((const Affine<Fq2c>*)d_bases, (uint32_t)n, d_bitmap, combine ? 1 : 0, d_count));
+    uint32_t h = 0;
+    UG_CUDA_CHECK(cudaMemcpyAsync(&h, d_count, 4, cudaMemcpyDeviceToHost, ctx.stream));
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+    return h;
+}
+
 void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d_index, uint64_t n, int force_c,
-                     const std::string& slot, MsmDigits& out, const MsmConfig* table_cfg) {
+                     const std::string& slot, MsmDigits& out, const MsmConfig* table_cfg, const uint32_t* d_skip) {
     ctx.activate();
     if (n >= (1ull << 31)) throw std::runtime_error("ultragroth_b200: MSM size must be < 2^31");
     MsmConfig cfg = table_cfg ? *table_cfg : msm_pick_config(n, force_c, false);
@@ -84,13 +98,13 @@ void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d
     UG_CUDA_CHECK(cudaMemsetAsync(counts, 0, (size_t)cfg.NB * 4, ctx.stream));
     if (n > 0) {
         int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-        UG_KERNEL(ctx, "k_digits_count", k_digits_count<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, key_stride, counts));
+        UG_KERNEL(ctx, "k_digits_count", k_digits_count<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, key_stride, counts, d_skip));
     }
     exclusive_scan_u32(ctx, counts, cfg.NB, out.starts, out.starts + cfg.NB, slot);
     UG_CUDA_CHECK(cudaMemcpyAsync(cursor, out.starts, (size_t)cfg.NB * 4, cudaMemcpyDeviceToDevice, ctx.stream));
     if (n > 0) {
         int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-        UG_KERNEL(ctx, "k_digits_scatter", k_digits_scatter<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, key_stride, entry_stride, cursor, out.entries));
+        UG_KERNEL(ctx, "k_digits_scatter", k_digits_scatter<<<blocks, 256, 0, ctx.stream>>>(d_scalars, d_index, n, cfg.c, cfg.W, key_stride, entry_stride, cursor, out.entries, d_skip));
     }
 }
 
@@ -138,9 +152,13 @@ template <class F>
 // nb base arrays that pair with the SAME sorted digits (A, B1, C of a proof) go through together: one accumulate launch each
 // into consecutive bucket sets, then ONE pass of the latency-bound tail (segmented merge, running sums, bit sums) over all of
 // them -- the tail's serial chains are paid once instead of nb times and its grids are nb times fuller.
-static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* const* d_bases_v, int nb, const MsmDigits& dg, const std::string* slots) {
+static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* const* d_bases_v, int nb, const MsmDigits* const* dgs, const std::string* slots) {
     ctx.activate();
+    // dgs[m]: the sorted digits array m pairs with (all with the same window config; they differ only in which points were skipped)
+    const MsmDigits& dg = *dgs[0];
     const MsmConfig& cfg = dg.cfg;
+    for (int m = 1; m < nb; m++)
+        if (dgs[m]->cfg.c != cfg.c || dgs[m]->cfg.NB != cfg.NB || dgs[m]->cfg.pre != cfg.pre) throw std::runtime_error("ultragroth_b200: MSM batch mixes window configurations");
     const bool g1 = sizeof(F) == 32;
     using P = XYZZ<F>;
     const uint32_t NBT = (uint32_t)nb * cfg.NB;  // buckets of the whole batch
@@ -165,7 +183,8 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* const* d_bases_v, i
         UG_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, acc_fn, 128, acc_smem));
     }
     occ = std::max(occ, 1);
-    uint64_t max_entries = dg.n * (uint64_t)cfg.W;
+    uint64_t max_entries = 0;
+    for (int m = 0; m < nb; m++) max_entries = std::max<uint64_t>(max_entries, dgs[m]->n * (uint64_t)cfg.W);
     uint64_t want_threads = std::max<uint64_t>(128, (max_entries + 15) / 16);
     uint32_t blocks = (uint32_t)std::min<uint64_t>((uint64_t)ctx.sm_count * occ, (want_threads + 127) / 128);
     uint32_t T = blocks * 128;
@@ -189,9 +208,9 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* const* d_bases_v, i
             uint4* suf_mem = (uint4*)ctx.workspace("msm.ba_suf", (size_t)T * (Lmax / 2 + 1) * sizeof(F));
             uint32_t* keys_mem = (uint32_t*)ctx.workspace("msm.ba_keys", (size_t)T * Lmax * 4);
             uint32_t* pairs_mem = (uint32_t*)ctx.workspace("msm.ba_pairs", (size_t)T * (Lmax / 2 + 1) * 4);
-            UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), ba_fn<<<blocks, BA_BS, 0, ctx.stream>>>(d_bases_v[m], dg.entries, dg.starts, cfg.NB, bk, pk, pp, key_off, NBT, Lmax, list_mem, suf_mem, keys_mem, pairs_mem));
+            UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), ba_fn<<<blocks, BA_BS, 0, ctx.stream>>>(d_bases_v[m], dgs[m]->entries, dgs[m]->starts, cfg.NB, bk, pk, pp, key_off, NBT, Lmax, list_mem, suf_mem, keys_mem, pairs_mem));
         } else {
-            UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), acc_fn<<<blocks, 128, acc_smem, ctx.stream>>>(d_bases_v[m], dg.entries, dg.starts, cfg.NB, bk, pk, pp, key_off, NBT));
+            UG_KERNEL(ctx, (g1 ? "k_accumulate<G1>" : "k_accumulate<G2>"), acc_fn<<<blocks, 128, acc_smem, ctx.stream>>>(d_bases_v[m], dgs[m]->entries, dgs[m]->starts, cfg.NB, bk, pk, pp, key_off, NBT));
         }
     }
 
@@ -252,23 +271,29 @@ static void msm_launch_impl(DeviceCtx& ctx, const Affine<F>* const* d_bases_v, i
         uint8_t* host = (uint8_t*)ctx.pinned("msm.sums." + slots[m], (size_t)64 * 32 * sizeof(P) + 16);
         UG_CUDA_CHECK(cudaMemcpy2DAsync(host, (size_t)nwin1 * sizeof(P), sums + (size_t)m * nwin1, (size_t)nwin * sizeof(P),
                                         (size_t)nwin1 * sizeof(P), (size_t)L, cudaMemcpyDeviceToHost, ctx.stream));
-        UG_CUDA_CHECK(cudaMemcpyAsync(host + bytes, dg.starts + cfg.NB, 4, cudaMemcpyDeviceToHost, ctx.stream));
+        UG_CUDA_CHECK(cudaMemcpyAsync(host + bytes, dgs[m]->starts + cfg.NB, 4, cudaMemcpyDeviceToHost, ctx.stream));
     }
     for (int m = 0; m < nb; m++) ctx.record("msm." + slots[m]);
 }
 
 void msm_g1_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot) {
     const G1Affine* b = (const G1Affine*)d_bases;
-    msm_launch_impl<Fq>(ctx, &b, 1, dg, &slot);
+    const MsmDigits* d = &dg;
+    msm_launch_impl<Fq>(ctx, &b, 1, &d, &slot);
+}
+void msm_g1_launch_batch(DeviceCtx& ctx, const void* const* d_bases, int count, const MsmDigits* const* dgs, const std::string* slots) {
+    if (count < 1 || count > 8) throw std::invalid_argument("ultragroth_b200: MSM batch of 1..8 base arrays");
+    msm_launch_impl<Fq>(ctx, (const G1Affine* const*)d_bases, count, dgs, slots);
 }
 void msm_g1_launch_batch(DeviceCtx& ctx, const void* const* d_bases, int count, const MsmDigits& dg, const std::string* slots) {
-    if (count < 1 || count > 8) throw std::invalid_argument("ultragroth_b200: MSM batch of 1..8 base arrays");
-    msm_launch_impl<Fq>(ctx, (const G1Affine* const*)d_bases, count, dg, slots);
+    const MsmDigits* d[8] = {&dg, &dg, &dg, &dg, &dg, &dg, &dg, &dg};
+    msm_g1_launch_batch(ctx, d_bases, count, d, slots);
 }
 void msm_g2_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot) {
     // every G2 kernel is instantiated on Fq2c (Fq2's layout, CALLED products): an inlined Fq2 kernel is 200-500 KB of SASS
     const Affine<Fq2c>* b = (const Affine<Fq2c>*)d_bases;
-    msm_launch_impl<Fq2c>(ctx, &b, 1, dg, &slot);
+    const MsmDigits* d = &dg;
+    msm_launch_impl<Fq2c>(ctx, &b, 1, &d, &slot);
 }
 
 // ---- resident window tables ----------------------------------------------------------------------

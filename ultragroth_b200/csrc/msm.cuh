@@ -84,9 +84,14 @@ UG_D Scalar256 load_scalar(const uint8_t* scalars, const uint32_t* index, uint64
 //   per-window bucket sets (ad-hoc bases):   key = w*B + |d|-1,  entry = i                 (key_stride = B, entry_stride = 0)
 //   one shared bucket set (precomputed 2^(c*w) multiples of every base, msm_build_table):
 //                                            key = |d|-1,        entry = w*n_bases + i     (key_stride = 0, entry_stride = n_bases)
+// skip: optional bitmap over the points (bit i set = base i is the point at infinity in EVERY array this sort serves): such points
+// get no digit entries at all, so the accumulation never sees them (a lane that meets an infinity base in k_accumulate idles
+// for a whole mixed addition while the rest of its warp works)
 __global__ void k_digits_count(const uint8_t* __restrict__ scalars, const uint32_t* __restrict__ index,
-                               uint64_t n, int c, int W, uint32_t key_stride, uint32_t* __restrict__ counts) {
+                               uint64_t n, int c, int W, uint32_t key_stride, uint32_t* __restrict__ counts,
+                               const uint32_t* __restrict__ skip) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        if (skip && ((skip[i >> 5] >> (i & 31)) & 1u)) continue;
         Scalar256 s = load_scalar(scalars, index, i);
         scalar_reduce(s);
         scalar_digits(s, c, W, [&](int w, uint32_t b, bool) { atomicAdd(&counts[(uint32_t)w * key_stride + b], 1u); });
@@ -95,8 +100,9 @@ __global__ void k_digits_count(const uint8_t* __restrict__ scalars, const uint32
 
 __global__ void k_digits_scatter(const uint8_t* __restrict__ scalars, const uint32_t* __restrict__ index,
                                  uint64_t n, int c, int W, uint32_t key_stride, uint32_t entry_stride,
-                                 uint32_t* __restrict__ cursor, uint32_t* __restrict__ entries) {
+                                 uint32_t* __restrict__ cursor, uint32_t* __restrict__ entries, const uint32_t* __restrict__ skip) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        if (skip && ((skip[i >> 5] >> (i & 31)) & 1u)) continue;
         Scalar256 s = load_scalar(scalars, index, i);
         scalar_reduce(s);
         scalar_digits(s, c, W, [&](int w, uint32_t b, bool neg) {
@@ -104,6 +110,34 @@ __global__ void k_digits_scatter(const uint8_t* __restrict__ scalars, const uint
             entries[pos] = ((uint32_t)i + (uint32_t)w * entry_stride) | (neg ? 0x80000000u : 0u);
         });
     }
+}
+
+// bitmap[i / 32] bit (i % 32) = 1 iff bases[i] is the point at infinity (AND-ed into an existing bitmap when `combine`); *count += set bits
+template <class F>
+__global__ void __launch_bounds__(256) k_inf_bitmap(const Affine<F>* __restrict__ bases, uint32_t n, uint32_t* __restrict__ bitmap, int combine,
+                                                    uint32_t* __restrict__ count) {
+    // one warp owns 32 consecutive points = one bitmap word
+    const uint32_t warps = (gridDim.x * blockDim.x) >> 5, wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    uint32_t local = 0;
+    for (uint32_t w = wid; w * 32 < n; w += warps) {
+        const uint32_t i = w * 32 + lane;
+        bool inf = false;
+        if (i < n) {
+            // the x and y coordinates are all-zero exactly for the point at infinity (zkey convention)
+            const uint4* p = reinterpret_cast<const uint4*>(&bases[i]);
+            uint32_t o = 0;
+#pragma unroll
+            for (int k = 0; k < (int)(sizeof(Affine<F>) / 16); k++) { uint4 v = __ldg(p + k); o |= v.x | v.y | v.z | v.w; }
+            inf = o == 0;
+        }
+        uint32_t word = __ballot_sync(0xffffffffu, inf);
+        if (lane == 0) {
+            if (combine) word &= bitmap[w];
+            bitmap[w] = word;
+            local += __popc(word);
+        }
+    }
+    if (lane == 0 && local) atomicAdd(count, local);
 }
 
 // ---- exclusive scan of the histogram (3 small launches; tile = 2048 counters) -----------------

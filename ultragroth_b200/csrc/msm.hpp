@@ -60,8 +60,12 @@ struct MsmDigits {
 // d_scalars: n (or max(index)+1) raw 32-byte little-endian scalars on the device; d_index optional gather
 // list (src/ultra_groth.cpp:415-419,439-445 folded into the scalar fetch).  `slot` names the workspace.
 // `table_cfg`: when the digits are meant for MsmTable bases, the table's config (window size and layout must match).
+// `d_skip`: optional bitmap of points that get NO entries (points at infinity of the arrays this sort serves, msm_inf_bitmap).
 void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d_index, uint64_t n, int force_c,
-                     const std::string& slot, MsmDigits& out, const MsmConfig* table_cfg = nullptr);
+                     const std::string& slot, MsmDigits& out, const MsmConfig* table_cfg = nullptr, const uint32_t* d_skip = nullptr);
+// bitmap of the points at infinity among n affine bases (group 1: G1, 2: G2); combine = AND into the existing bitmap (points that
+// are infinite in ALL the arrays combined).  Returns the number of set bits.  d_bitmap: (n + 31) / 32 words, device.
+uint64_t msm_inf_bitmap(DeviceCtx& ctx, int group, const void* d_bases, uint64_t n, uint32_t* d_bitmap, bool combine);
 
 // Bucket accumulation + bucket reduction on the device for one base array, final Horner on the host.
 void msm_accumulate_g1(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, HG1XYZZ* out);
@@ -75,6 +79,8 @@ void msm_g1_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, con
 void msm_g1_finish(DeviceCtx& ctx, const MsmDigits& dg, const std::string& slot, HG1XYZZ* out);
 // `count` base arrays (tables) that pair with the same digits: separate accumulations, ONE shared reduction tail; finish per slot
 void msm_g1_launch_batch(DeviceCtx& ctx, const void* const* d_bases, int count, const MsmDigits& dg, const std::string* slots);
+// the same with one digit set PER base array (same window config): arrays whose infinity patterns differ are sorted separately
+void msm_g1_launch_batch(DeviceCtx& ctx, const void* const* d_bases, int count, const MsmDigits* const* dgs, const std::string* slots);
 void msm_g2_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot);
 void msm_g2_finish(DeviceCtx& ctx, const MsmDigits& dg, const std::string& slot, HG2XYZZ* out);
 

@@ -429,6 +429,7 @@ public:
         final_msms(commit, rk, nullptr, commit_aff, m);
         finish(m, rk, commit_aff, stringProof, stringPublic);
     }
+    HG1Affine shard_commit_aff;  // sharded v2: the blinded round commitment between ugb_shard_lookup and ugb_shard_finish
     unsigned long long proofBufferMinSize() const { return ProofBufferMinSizeUltraGroth(); }
     unsigned long long publicBufferMinSize() const { return PublicBufferMinSize((unsigned long long)hdr.nPublic - 1); }
 
@@ -713,6 +714,11 @@ int ugb_prover_create_times(void* prover_object, double* out4) {
     for (int i = 0; i < 4; i++) out4[i] = static_cast<ProverBase*>(prover_object)->dev->create_ms[i];
     return UGB_OK;
 }
+int ugb_prover_inf_points(void* prover_object, uint64_t* out3) {
+    if (!prover_object || !out3) return UGB_ERROR;
+    for (int i = 0; i < 3; i++) out3[i] = static_cast<ProverBase*>(prover_object)->dev->inf_points[i];
+    return UGB_OK;
+}
 // One WHOLE proof from the witness (and, UltraGroth, lookup arrays) left in HBM by the previous *_prover_prove call: both rounds,
 // challenge, lookup fill, every MSM, the H pipeline, blinding, assembly and JSON -- everything except the host->device input copy.
 // The proof is kept and can be read back with ugb_prover_last_proof.
@@ -811,6 +817,105 @@ int ugb_ultra_groth_prove_raw(void* prover_object, void* wtns_signals, const uin
     HG2Affine B;
     static_cast<UltraGrothProver*>(b)->prove_raw((const uint8_t*)wtns_signals, lk, A, B, C, R, (uint8_t*)wtns_signals);
     memcpy(out_A64, &A, 64); memcpy(out_B128, &B, 128); memcpy(out_final_commitment64, &C, 64); memcpy(out_round_commitment64, &R, 64);
+    API_CATCH_PROVE
+}
+
+// ---- sharded proving, phase by phase (declared in include/ultragroth_b200.h) ----
+int ugb_shard_layout_get(void* prover_object, ugb_shard_layout* out) {
+    EXT_TRY
+    if (!prover_object || !out) throw std::invalid_argument("Null argument");
+    ProverDevice& d = *static_cast<ProverBase*>(prover_object)->dev;
+    out->w = d.dev_w(); out->a = d.dev_a(); out->b = d.dev_b(); out->c = d.dev_c();
+    out->nVars = d.nVars; out->domainSize = d.domainSize;
+    out->w_chunk = d.w_chunk(); out->h_chunk = d.h_chunk();
+    out->rank = d.shard_rank(); out->world = d.shard_world();
+    out->device = d.ctx().device;
+    out->stream = (void*)d.ctx().stream;
+    EXT_CATCH
+}
+int ugb_shard_upload_slice(void* prover_object, const void* wtns_buffer, unsigned long long wtns_size, char* error_msg,
+                           unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !wtns_buffer) throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    if (b->is_ultra()) {
+        UltraGrothProver* p = static_cast<UltraGrothProver*>(b);
+        BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
+        UltraGrothProver::Lookup lk;
+        const uint8_t* w = p->check_witness(wtns, lk);
+        b->dev->upload_witness_slice(w);
+        p->stage(lk);
+    } else {
+        b->dev->upload_witness_slice(static_cast<Groth16Prover*>(b)->check_witness(wtns_buffer, wtns_size));
+    }
+    API_CATCH_PROVE
+}
+int ugb_shard_round_partial(void* prover_object, void* round_partial_out128, char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !round_partial_out128) throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    if (!b->is_ultra()) throw std::invalid_argument("not an ultragroth prover");
+    HG1XYZZ part;
+    b->dev->ultra_round_msm(part);
+    memcpy(round_partial_out128, &part, sizeof(part));
+    API_CATCH_PROVE
+}
+int ugb_shard_lookup(void* prover_object, const void* round_partials, uint32_t count, const void* rk32, char* error_msg,
+                     unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !round_partials || !rk32 || count == 0) throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    if (!b->is_ultra()) throw std::invalid_argument("not an ultragroth prover");
+    UltraGrothProver* p = static_cast<UltraGrothProver*>(b);
+    std::vector<HG1XYZZ> rp(count);
+    memcpy(rp.data(), round_partials, (size_t)count * sizeof(HG1XYZZ));
+    HG1XYZZ commit = rp[0];
+    for (uint32_t i = 1; i < count; i++) pt_add(commit, rp[i]);
+    Scalar rk;
+    memcpy(&rk, rk32, 32);
+    pt_add(commit, pt_mul(from_affine_bytes<HFq>(p->hdr.final_delta1), rk));  // src/ultra_groth.cpp:161-184
+    p->shard_commit_aff = pt_to_affine(commit);
+    b->dev->ultra_lookup_apply(UltraGrothProver::derive_challenge(p->shard_commit_aff));
+    API_CATCH_PROVE
+}
+int ugb_shard_h_transform(void* prover_object, int vector_mask, char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object) throw std::invalid_argument("Null prover object");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    b->dev->phase_h_transform(vector_mask & 7);
+    API_CATCH_PROVE
+}
+int ugb_shard_witness_msms(void* prover_object, char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object) throw std::invalid_argument("Null prover object");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    b->dev->phase_witness_msms();
+    API_CATCH_PROVE
+}
+int ugb_shard_h_msm(void* prover_object, char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object) throw std::invalid_argument("Null prover object");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    b->dev->phase_h_msm(false);
+    API_CATCH_PROVE
+}
+int ugb_shard_finish(void* prover_object, void* partial_out, char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object || !partial_out) throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    ProofMsms m;
+    b->dev->phase_finish(m);
+    // UltraGroth: round_c carries the blinded commitment to the assembling rank (identical on every shard)
+    if (b->is_ultra()) m.round_c = XYZZ<HFq>::from_affine(static_cast<UltraGrothProver*>(b)->shard_commit_aff);
+    else m.round_c = HG1XYZZ::inf();
+    memcpy(partial_out, &m, sizeof(m));
     API_CATCH_PROVE
 }
 

@@ -301,6 +301,8 @@ ProverDevice::ProverDevice(int device, const ZkeyData& zk, uint32_t shard_rank, 
 
 void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t shard_world, bool tables) {
     const double t_begin = now_ms();
+    shard_rank_ = shard_rank;
+    shard_world_ = shard_world;
     shard_range(nVars, shard_world, shard_rank, w_lo_, w_hi_);
     shard_range(domainSize, shard_world, shard_rank, h_lo_, h_hi_);
     const uint64_t wn = w_hi_ - w_lo_, hn = h_hi_ - h_lo_;
@@ -391,6 +393,25 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
         H_ = upload(ctx, zk.H + h_lo_ * 64, (size_t)hn * 64);
     }
     UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+    // zero-point maps: which witness-paired bases are the point at infinity (their polynomial vanishes at tau: signals that never
+    // occur in that matrix).  A class with enough of them gets its own digit sort without those points: an infinity base costs its
+    // lane a whole idle mixed addition in k_accumulate, a skipped digit costs nothing.  G1-only classes need >= 15 % to repay the
+    // extra sort, the class holding the G2 array >= 4 %.
+    {
+        const char* e = getenv("UGB_MSM_SKIP_INF");
+        const bool enabled = !(e && atoi(e) == 0) && wn > 0;
+        const size_t words = (size_t)((wn + 31) / 32) * 4 + 16;
+        auto classify = [&](uint32_t*& skip, uint64_t& count, const void* g1a, const void* g2a, double thr) {
+            uint32_t* bm = (uint32_t*)dev_alloc(words);
+            count = msm_inf_bitmap(ctx, 1, g1a, wn, bm, false);
+            if (g2a) count = msm_inf_bitmap(ctx, 2, g2a, wn, bm, true);
+            if (enabled && (double)count >= thr * (double)wn) skip = bm;
+            else UG_CUDA_CHECK(cudaFree(bm));
+        };
+        classify(skip_a_, inf_points[0], A_, nullptr, 0.15);
+        classify(skip_b_, inf_points[1], B1_, B2_, 0.04);
+        if (c_shares_witness_sort_) classify(skip_c_, inf_points[2], C_, nullptr, 0.15);
+    }
     create_ms[0] = now_ms() - t_begin;
 
     // window tables: 2^(c*w) multiples of every base, resident next to the bases they replace (UGB_MSM_PRE=0: off)
@@ -433,10 +454,11 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
     coef_val_ = upload(ctx, csr.val.data(), csr.val.size());
     UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
 
-    w_ = dev_alloc((size_t)nVars * 32);
-    a_ = dev_alloc((size_t)domainSize * 32);
-    b_ = dev_alloc((size_t)domainSize * 32);
-    c_ = dev_alloc((size_t)domainSize * 32);
+    w_ = dev_alloc((size_t)w_chunk() * shard_world_ * 32);  // padded so that equal-sized slices can be all-gathered in place
+    // padded like w_: slices of the transformed vectors travel between shards in equal chunks
+    a_ = dev_alloc((size_t)h_chunk() * shard_world_ * 32);
+    b_ = dev_alloc((size_t)h_chunk() * shard_world_ * 32);
+    c_ = dev_alloc((size_t)h_chunk() * shard_world_ * 32);
     // twiddles resident before the first proof
     tabs_->stage_roots(false);
     tabs_->stage_roots(true);
@@ -455,6 +477,7 @@ void ProverDevice::release() {
     cudaSetDevice(ctx_->device);
     cudaStreamSynchronize(ctx_->stream);
     void** ptrs[] = {&long_rows_, &long_segs_, &long_partial_, &A_, &B1_, &B2_, &C_, &H_, &C1_, (void**)&idx_c1_, (void**)&idx_c2_, (void**)&row_ptr_,
+                     (void**)&skip_a_, (void**)&skip_b_, (void**)&skip_c_,
                      (void**)&coef_sig_, &coef_val_, &w_, &a_, &b_, &c_};
     for (void** p : ptrs) if (*p) { cudaFree(*p); *p = nullptr; }
     for (auto& e : ev_) if (e) cudaEventDestroy(e);
@@ -477,70 +500,117 @@ void ProverDevice::download_witness(uint8_t* dst, uint64_t first, uint64_t count
     UG_CUDA_CHECK(cudaStreamSynchronize(ctx_->stream));
 }
 
-// Everything from the (device-resident) witness to the five MSM results.
-void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
+// Everything from the (device-resident) witness to the five MSM results, in four phases that the sharded prover (several GPUs, one
+// point range each) interleaves with its exchanges; one GPU runs them back to back.  Stage-clock events: 0 start, 1 sorts, 2-5 the
+// witness MSMs, 6 SpMV, 7 iNTT + coset, 8 NTT, 9 pointwise, 10 H sort, 11 H MSM.
+void ProverDevice::mark_stage(int idx) {
+    if (timing) UG_CUDA_CHECK(cudaEventRecord(ev_[idx], ctx_->stream));
+}
+
+// phase 1: digit sorts of the witness slice + the A, B1, B2, C bucket MSMs (enqueued, not waited for)
+void ProverDevice::phase_witness_msms() {
     DeviceCtx& ctx = *ctx_;
-    const uint32_t n = domainSize;
-    int e = 0;
-    auto mark = [&]() { if (timing) UG_CUDA_CHECK(cudaEventRecord(ev_[e++], ctx.stream)); };
-    mark();  // 0
-    // the four witness MSMs share one digit sort (src/groth16.cpp:53-64 all read the same scalars)
-    MsmDigits dw;
-    msm_sort_digits(ctx, (const uint8_t*)w_ + w_lo_ * 32, nullptr, w_hi_ - w_lo_, 0, "w", dw, pre_ ? &cfg_w_ : nullptr);
-    mark();  // 1
-    MsmDigits dc;
+    ctx.activate();
+    Phase& ph = ph_;
+    ph = Phase();
+    mark_stage(0);
+    // the four witness MSMs read the same scalars (src/groth16.cpp:53-64): ONE digit sort serves every array that has no zero-point
+    // map of its own; arrays with many points at infinity get a sort that skips them (skip_a_ / skip_b_ / skip_c_)
+    const uint8_t* wsl = (const uint8_t*)w_ + w_lo_ * 32;
+    const uint64_t wn = w_hi_ - w_lo_;
+    const MsmConfig* wcfg = pre_ ? &cfg_w_ : nullptr;
+    const bool c_in_w = c_shares_witness_sort_;
+    if (!skip_a_ || !skip_b_ || (c_in_w && !skip_c_)) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "w", ph.dw, wcfg);
+    if (skip_a_) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wa", ph.dwa, wcfg, skip_a_);
+    if (skip_b_) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wb", ph.dwb, wcfg, skip_b_);
+    if (c_in_w && skip_c_) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wc", ph.dwc, wcfg, skip_c_);
+    ph.dA = skip_a_ ? &ph.dwa : &ph.dw;
+    ph.dB = skip_b_ ? &ph.dwb : &ph.dw;
+    ph.dC = c_in_w ? (skip_c_ ? &ph.dwc : &ph.dw) : &ph.dc;
+    mark_stage(1);
     static const bool batch_abc = !(getenv("UGB_MSM_BATCH") && atoi(getenv("UGB_MSM_BATCH")) == 0);
-    if (c_shares_witness_sort_ && batch_abc) {
-        // A, B1 and C multiply the same witness: one shared reduction tail (msm_g1_launch_batch); the stage clock is split evenly
+    ph.batched = c_in_w && batch_abc;
+    if (ph.batched) {
+        // A, B1 and C go through together: one shared reduction tail (msm_g1_launch_batch); the stage clock is split evenly
         const void* bases[3] = {A_, B1_, C_};
+        const MsmDigits* dgs[3] = {ph.dA, ph.dB, ph.dC};
         const std::string slots[3] = {"a", "b1", "c"};
-        msm_g1_launch_batch(ctx, bases, 3, dw, slots);
-        mark();  // 2
-        mark();  // 3
-        msm_g2_launch(ctx, B2_, dw, "b2");
-        mark();  // 4
+        msm_g1_launch_batch(ctx, bases, 3, dgs, slots);
+        mark_stage(2);
+        mark_stage(3);
+        msm_g2_launch(ctx, B2_, *ph.dB, "b2");
+        mark_stage(4);
     } else {
-        msm_g1_launch(ctx, A_, dw, "a");
-        mark();  // 2
-        msm_g1_launch(ctx, B1_, dw, "b1");
-        mark();  // 3
-        msm_g2_launch(ctx, B2_, dw, "b2");
-        mark();  // 4
-        if (c_shares_witness_sort_) {
-            msm_g1_launch(ctx, C_, dw, "c");
+        msm_g1_launch(ctx, A_, *ph.dA, "a");
+        mark_stage(2);
+        msm_g1_launch(ctx, B1_, *ph.dB, "b1");
+        mark_stage(3);
+        msm_g2_launch(ctx, B2_, *ph.dB, "b2");
+        mark_stage(4);
+        if (c_in_w) {
+            msm_g1_launch(ctx, C_, *ph.dC, "c");
         } else {
-            msm_sort_digits(ctx, (const uint8_t*)w_, idx_c2_, n_c2_, 0, "cidx", dc, pre_ ? &cfg_c2_ : nullptr);
-            msm_g1_launch(ctx, C_, dc, "c");
+            msm_sort_digits(ctx, (const uint8_t*)w_, idx_c2_, n_c2_, 0, "cidx", ph.dc, pre_ ? &cfg_c2_ : nullptr);
+            msm_g1_launch(ctx, C_, ph.dc, "c");
         }
     }
-    mark();  // 5
-    // H pipeline
-    int blocks = (int)std::min<uint64_t>(((uint64_t)n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-    UG_KERNEL(ctx, "k_spmv_abc", k_spmv_abc<<<blocks, 256, 0, ctx.stream>>>(row_ptr_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, n, (Fr*)a_, (Fr*)b_, (Fr*)c_));
-    if (n_long_) {
-        UG_KERNEL(ctx, "k_spmv_long", k_spmv_long<<<n_long_segs_, SPMV_LONG_BS, 0, ctx.stream>>>((const LongRow*)long_segs_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, (Fr*)long_partial_));
-        UG_KERNEL(ctx, "k_spmv_long_finish", k_spmv_long_finish<<<n_long_, SPMV_LONG_BS, 0, ctx.stream>>>((const LongRow*)long_rows_, (const Fr*)long_partial_, n, (Fr*)a_, (Fr*)b_));
-        UG_KERNEL(ctx, "k_spmv_fix_c", k_spmv_fix_c<<<(n_long_ + 127) / 128, 128, 0, ctx.stream>>>((const LongRow*)long_rows_, n_long_, n, (const Fr*)a_, (const Fr*)b_, (Fr*)c_));
+    mark_stage(5);
+}
+
+// phase 2: a, b, c = A w, B w, (A w) o (B w) (src/groth16.cpp:66-108), then ifft -> coset shift -> fft (:110-140) of the vectors
+// selected by `mask` (bit 0: a, bit 1: b, bit 2: c).  A shard that owns no vector passes 0 and only keeps the stage clock in step.
+void ProverDevice::phase_h_transform(int mask) {
+    DeviceCtx& ctx = *ctx_;
+    ctx.activate();
+    const uint32_t n = domainSize;
+    if (mask & 7) {
+        int blocks = (int)std::min<uint64_t>(((uint64_t)n + 255) / 256, (uint64_t)ctx.sm_count * 8);
+        UG_KERNEL(ctx, "k_spmv_abc", k_spmv_abc<<<blocks, 256, 0, ctx.stream>>>(row_ptr_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, n, (Fr*)a_, (Fr*)b_, (Fr*)c_));
+        if (n_long_) {
+            UG_KERNEL(ctx, "k_spmv_long", k_spmv_long<<<n_long_segs_, SPMV_LONG_BS, 0, ctx.stream>>>((const LongRow*)long_segs_, coef_sig_, (const Fr*)coef_val_, (const Fr*)w_, (Fr*)long_partial_));
+            UG_KERNEL(ctx, "k_spmv_long_finish", k_spmv_long_finish<<<n_long_, SPMV_LONG_BS, 0, ctx.stream>>>((const LongRow*)long_rows_, (const Fr*)long_partial_, n, (Fr*)a_, (Fr*)b_));
+            UG_KERNEL(ctx, "k_spmv_fix_c", k_spmv_fix_c<<<(n_long_ + 127) / 128, 128, 0, ctx.stream>>>((const LongRow*)long_rows_, n_long_, n, (const Fr*)a_, (const Fr*)b_, (Fr*)c_));
+        }
     }
-    mark();  // 6
-    Fr* vecs[3] = {(Fr*)a_, (Fr*)b_, (Fr*)c_};
+    mark_stage(6);
+    Fr* all[3] = {(Fr*)a_, (Fr*)b_, (Fr*)c_};
+    Fr* vecs[3] = {nullptr, nullptr, nullptr};
+    int count = 0;
+    for (int v = 0; v < 3; v++) if (mask & (1 << v)) vecs[count++] = all[v];
     // ifft + coset shift (+ 1/n) fused, output bit-reversed; then fft from bit-reversed to natural
-    ntt_run(ctx, *tabs_, vecs, 3, logn, NTT_NATURAL_TO_BITREV, true, tabs_->coset_inv_bitrev(logn), nullptr);
-    mark();  // 7
-    ntt_run(ctx, *tabs_, vecs, 3, logn, NTT_BITREV_TO_NATURAL, false, nullptr, nullptr);
-    mark();  // 8
-    UG_KERNEL(ctx, "k_h_final", k_h_final<<<blocks, 256, 0, ctx.stream>>>((Fr*)a_, (const Fr*)b_, (const Fr*)c_, n));
-    mark();  // 9
-    MsmDigits dh;
-    msm_sort_digits(ctx, (const uint8_t*)a_ + h_lo_ * 32, nullptr, h_hi_ - h_lo_, 0, "h", dh, pre_ ? &cfg_h_ : nullptr);
-    mark();  // 10
-    msm_g1_launch(ctx, H_, dh, "h");
-    mark();  // 11
-    msm_g1_finish(ctx, dw, "a", &out.a);
-    msm_g1_finish(ctx, dw, "b1", &out.b1);
-    msm_g2_finish(ctx, dw, "b2", &out.b2);
-    msm_g1_finish(ctx, c_shares_witness_sort_ ? dw : dc, "c", &out.c);
-    msm_g1_finish(ctx, dh, "h", &out.h);
+    if (count) ntt_run(ctx, *tabs_, vecs, count, logn, NTT_NATURAL_TO_BITREV, true, tabs_->coset_inv_bitrev(logn), nullptr);
+    mark_stage(7);
+    if (count) ntt_run(ctx, *tabs_, vecs, count, logn, NTT_BITREV_TO_NATURAL, false, nullptr, nullptr);
+    mark_stage(8);
+}
+
+// phase 3: h = fromMontgomery(a*b - c) (:142-148) and the H MSM over this shard's range.  whole_h: form all domainSize scalars
+// (one GPU; also what the ugb_prover_last_h tap reads) instead of only [h_lo_, h_hi_).
+void ProverDevice::phase_h_msm(bool whole_h) {
+    DeviceCtx& ctx = *ctx_;
+    ctx.activate();
+    const uint64_t lo = whole_h ? 0 : h_lo_, cnt = whole_h ? domainSize : h_hi_ - h_lo_;
+    if (cnt) {
+        int blocks = (int)std::min<uint64_t>((cnt + 255) / 256, (uint64_t)ctx.sm_count * 8);
+        UG_KERNEL(ctx, "k_h_final", k_h_final<<<blocks, 256, 0, ctx.stream>>>((Fr*)a_ + lo, (const Fr*)b_ + lo, (const Fr*)c_ + lo, (uint32_t)cnt));
+    }
+    mark_stage(9);
+    msm_sort_digits(ctx, (const uint8_t*)a_ + h_lo_ * 32, nullptr, h_hi_ - h_lo_, 0, "h", ph_.dh, pre_ ? &cfg_h_ : nullptr);
+    mark_stage(10);
+    msm_g1_launch(ctx, H_, ph_.dh, "h");
+    mark_stage(11);
+}
+
+// phase 4: wait for the partial sums and finish them on the host
+void ProverDevice::phase_finish(ProofMsms& out) {
+    DeviceCtx& ctx = *ctx_;
+    ctx.activate();
+    Phase& ph = ph_;
+    msm_g1_finish(ctx, *ph.dA, "a", &out.a);
+    msm_g1_finish(ctx, *ph.dB, "b1", &out.b1);
+    msm_g2_finish(ctx, *ph.dB, "b2", &out.b2);
+    msm_g1_finish(ctx, *ph.dC, "c", &out.c);
+    msm_g1_finish(ctx, ph.dh, "h", &out.h);
     check_lookup_error();  // the flag travelled before the MSM results on the same stream
     ctx.prof_collect();
     if (timing) {
@@ -548,12 +618,28 @@ void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
         float* dst[] = {&last_times.sort_w, &last_times.msm_a, &last_times.msm_b1, &last_times.msm_b2, &last_times.msm_c, &last_times.spmv,
                         &last_times.intt, &last_times.ntt, &last_times.hfinal, &last_times.sort_h, &last_times.msm_h};
         for (int i = 0; i < 11; i++) UG_CUDA_CHECK(cudaEventElapsedTime(dst[i], ev_[i], ev_[i + 1]));
-        if (c_shares_witness_sort_ && batch_abc) {  // the batched A/B1/C launch was timed as one interval (recorded under msm_a)
+        if (ph.batched) {  // the batched A/B1/C launch was timed as one interval (recorded under msm_a)
             const float each = last_times.msm_a / 3.0f;
             last_times.msm_a = last_times.msm_b1 = last_times.msm_c = each;
         }
         UG_CUDA_CHECK(cudaEventElapsedTime(&last_times.total, ev_[0], ev_[11]));
     }
+}
+
+void ProverDevice::h_pipeline_and_msms(ProofMsms& out, bool ultra) {
+    (void)ultra;
+    phase_witness_msms();
+    phase_h_transform(7);
+    phase_h_msm(true);
+    phase_finish(out);
+}
+
+// sharded v2, phase 0: only this shard's slice of the witness crosses PCIe; the caller then all-gathers the slices between the
+// GPUs (NVLink) into every shard's full copy (w_ is padded to world * w_chunk signals for that)
+void ProverDevice::upload_witness_slice(const uint8_t* witness) {
+    ctx_->activate();
+    if (w_hi_ > w_lo_)
+        UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)w_ + w_lo_ * 32, witness + w_lo_ * 32, (size_t)(w_hi_ - w_lo_) * 32, cudaMemcpyHostToDevice, ctx_->stream));
 }
 
 void ProverDevice::prove_groth16(const uint8_t* witness, ProofMsms& out) {

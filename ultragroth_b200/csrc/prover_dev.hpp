@@ -50,11 +50,29 @@ public:
     // witness, the coefficients and the H pipeline are replicated on every shard.
     // tables = false: skip the window-table build (one-shot *_prover calls: the 2^(c*k) multiples only pay off across proofs)
     ProverDevice(int device, const ZkeyData& zk, uint32_t shard_rank = 0, uint32_t shard_world = 1, bool tables = true);
+    // slice `rank` of [0, n): equal chunks of ceil(n / world) (the last ones may be short or empty), so that slices can be exchanged
+    // with equal-sized all-gather / scatter collectives
+    static uint64_t shard_chunk(uint64_t n, uint32_t world) { return (n + world - 1) / world; }
     static void shard_range(uint64_t n, uint32_t world, uint32_t rank, uint64_t& lo, uint64_t& hi) {
-        const uint64_t base = n / world, rem = n % world;
-        lo = rank * base + std::min<uint64_t>(rank, rem);
-        hi = lo + base + (rank < rem ? 1 : 0);
+        const uint64_t chunk = shard_chunk(n, world);
+        lo = std::min<uint64_t>(n, rank * chunk);
+        hi = std::min<uint64_t>(n, lo + chunk);
     }
+    uint64_t w_chunk() const { return shard_chunk(nVars, shard_world_); }
+    uint64_t h_chunk() const { return shard_chunk(domainSize, shard_world_); }
+    uint32_t shard_rank() const { return shard_rank_; }
+    uint32_t shard_world() const { return shard_world_; }
+    void* dev_w() const { return w_; }
+    void* dev_a() const { return a_; }
+    void* dev_b() const { return b_; }
+    void* dev_c() const { return c_; }
+
+    // ---- the proof in phases (the sharded prover interleaves its exchanges between them; see prover_dev.cu) ----
+    void upload_witness_slice(const uint8_t* witness);
+    void phase_witness_msms();
+    void phase_h_transform(int mask);
+    void phase_h_msm(bool whole_h);
+    void phase_finish(ProofMsms& out);
     ~ProverDevice();
     double create_ms[4] = {0, 0, 0, 0};  // create-time breakdown: base uploads, coefficient CSR, window tables, total
 
@@ -89,6 +107,13 @@ public:
     int logn;
 
 private:
+    struct Phase {  // sorted digits of the proof in flight (they point into named workspaces)
+        MsmDigits dw, dwa, dwb, dwc, dc, dh;
+        const MsmDigits *dA = nullptr, *dB = nullptr, *dC = nullptr;
+        bool batched = false;
+    } ph_;
+    uint32_t shard_rank_ = 0, shard_world_ = 1;
+    void mark_stage(int idx);
     void construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t shard_world, bool tables);
     void release();
     void h_pipeline_and_msms(ProofMsms& out, bool ultra);
@@ -107,6 +132,12 @@ private:
     bool pre_ = false;
     MsmConfig cfg_w_, cfg_h_, cfg_c1_, cfg_c2_;
     uint32_t *idx_c1_ = nullptr, *idx_c2_ = nullptr;
+    // bitmaps of the points at infinity among the witness-paired bases (null: too few to pay for a sort of their own): an array whose
+    // polynomial is zero for many signals (B in most circuits) gets its own digit sort that skips them
+    uint32_t *skip_a_ = nullptr, *skip_b_ = nullptr, *skip_c_ = nullptr;
+public:
+    uint64_t inf_points[3] = {0, 0, 0};  // points at infinity in A, in B1 and B2 together, in the padded C (this shard's range)
+private:
     // coefficient matrix, CSR by (matrix, row)
     uint32_t* row_ptr_ = nullptr;  // [2n + 1]
     uint32_t* coef_sig_ = nullptr;

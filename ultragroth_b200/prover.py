@@ -132,6 +132,11 @@ class Prover:
         lib().ugb_prover_create_times(self.handle, arr)
         return dict(zip(("upload_ms", "csr_ms", "tables_ms", "total_ms"), [float(x) for x in arr]))
 
+    def inf_points(self):
+        arr = (ctypes.c_uint64 * 3)()
+        lib().ugb_prover_inf_points(self.handle, arr)
+        return {"a": int(arr[0]), "b": int(arr[1]), "c": int(arr[2])}
+
     def prove_resident(self):
         """One whole proof from the witness (and lookup arrays) already in HBM: no host->device input copy.  -> (proof, public)"""
         rc = lib().ugb_prover_prove_resident(self.handle)

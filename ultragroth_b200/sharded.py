@@ -9,12 +9,145 @@ from ._lib import check, lib
 
 
 def shard_range(n, world, rank):
-    """Contiguous slice of [0, n) owned by `rank`; sizes differ by at most one and cover [0, n) exactly."""
+    """Contiguous slice of [0, n) owned by `rank`: equal chunks of ceil(n / world) (the last ones may be short or empty), covering
+    [0, n) exactly -- equal chunks so that slices can travel in equal-sized all-gather / scatter collectives."""
     if world <= 0 or not 0 <= rank < world:
         raise ValueError("bad world/rank")
-    base, rem = divmod(n, world)
-    lo = rank * base + min(rank, rem)
-    return lo, lo + base + (1 if rank < rem else 0)
+    chunk = -(-n // world)
+    lo = min(n, rank * chunk)
+    return lo, min(n, lo + chunk)
+
+
+class ShardLayout(ctypes.Structure):
+    """ugb_shard_layout (include/ultragroth_b200.h)"""
+    _fields_ = [("w", ctypes.c_void_p), ("a", ctypes.c_void_p), ("b", ctypes.c_void_p), ("c", ctypes.c_void_p),
+                ("nVars", ctypes.c_uint64), ("domainSize", ctypes.c_uint64), ("w_chunk", ctypes.c_uint64), ("h_chunk", ctypes.c_uint64),
+                ("rank", ctypes.c_uint32), ("world", ctypes.c_uint32), ("device", ctypes.c_int), ("stream", ctypes.c_void_p)]
+
+
+def vector_owner(v, world):
+    """Which rank transforms vector v (0: a, 1: b, 2: c) of the H pipeline (src/groth16.cpp:110-140: three independent transforms).
+    world >= 3: ranks 0, 1, 2; world == 2: rank 0 takes a and b, rank 1 takes c; world == 1: rank 0 takes all."""
+    if world >= 3:
+        return v
+    if world == 2:
+        return 1 if v == 2 else 0
+    return 0
+
+
+def vector_mask(rank, world):
+    return sum(1 << v for v in range(3) if vector_owner(v, world) == rank)
+
+
+class _RawCuda:
+    """CUDA array interface over a raw device pointer (so torch can alias the prover's own buffers, no copies)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+def device_view(ptr, nbytes, device):
+    import torch
+    return torch.as_tensor(_RawCuda(ptr, nbytes), device=torch.device("cuda", device))
+
+
+class DistComm:
+    """The exchanges of ShardedProver.prove2 over torch.distributed (NCCL, NVLink / NVSwitch) on tensors that ALIAS the prover's device
+    buffers, enqueued against the prover's own stream -- no staging copies and no host synchronisation:
+      * all_gather_witness: in-place all-gather of the equal-sized witness slices (every rank ends with the whole witness in HBM
+        although only 1 / world of it crossed PCIe on each rank);
+      * scatter_vectors: the owner of a', b', c' sends rank j its point range; one batched group of NCCL send / recv, asynchronous,
+        so the witness MSMs run while the slices travel."""
+
+    def __init__(self, sp):
+        import torch
+        self.torch = torch
+        self.sp = sp
+        lay = sp.layout()
+        self.lay = lay
+        dev = lay.device
+        self.stream = torch.cuda.ExternalStream(lay.stream, device=torch.device("cuda", dev))
+        self.w = device_view(lay.w, lay.w_chunk * lay.world * 32, dev)
+        self.vec = [device_view(p, lay.h_chunk * lay.world * 32, dev) for p in (lay.a, lay.b, lay.c)]
+
+    def stream_scope(self):
+        return self.torch.cuda.stream(self.stream)
+
+    def all_gather_witness(self):
+        import torch.distributed as dist
+        lay = self.lay
+        if lay.world == 1:
+            return
+        cb = lay.w_chunk * 32
+        dist.all_gather_into_tensor(self.w, self.w[lay.rank * cb:(lay.rank + 1) * cb])
+
+    def scatter_vectors(self):
+        import torch.distributed as dist
+        lay = self.lay
+        if lay.world == 1:
+            return []
+        cb = lay.h_chunk * 32
+        ops = []
+        for v in range(3):
+            owner = vector_owner(v, lay.world)
+            if lay.rank == owner:
+                for j in range(lay.world):
+                    if j != owner:
+                        ops.append(dist.P2POp(dist.isend, self.vec[v][j * cb:(j + 1) * cb], j))
+            else:
+                ops.append(dist.P2POp(dist.irecv, self.vec[v][lay.rank * cb:(lay.rank + 1) * cb], owner))
+        return dist.batch_isend_irecv(ops) if ops else []
+
+    def wait(self, pending):
+        for req in pending:
+            req.wait()
+
+
+def prove_local(shards, wtns, rk=None):
+    """The prove2 protocol over shards that live in THIS process (one GPU holding several shards in the tests, or one process driving
+    several GPUs): the exchanges are plain device-to-device copies between the shards' buffers."""
+    import torch
+    world = len(shards)
+    lays = [s.layout() for s in shards]
+    W = [device_view(l.w, l.w_chunk * l.world * 32, l.device) for l in lays]
+    V = [[device_view(p, l.h_chunk * l.world * 32, l.device) for p in (l.a, l.b, l.c)] for l in lays]
+    streams = [torch.cuda.ExternalStream(l.stream, device=torch.device("cuda", l.device)) for l in lays]
+
+    def sync_all():
+        for st in streams:
+            st.synchronize()
+        torch.cuda.synchronize()
+
+    for s in shards:
+        s.upload_slice(wtns)
+    sync_all()
+    cb = lays[0].w_chunk * 32
+    for src in range(world):
+        for dst in range(world):
+            if dst != src:
+                W[dst][src * cb:(src + 1) * cb].copy_(W[src][src * cb:(src + 1) * cb])
+    sync_all()
+    ultra = shards[0].ultra
+    if ultra:
+        rounds = [s.round_partial_resident() for s in shards]
+        for s in shards:
+            s.lookup(rounds, rk)
+    for r, s in enumerate(shards):
+        s.h_transform(vector_mask(r, world))
+    sync_all()
+    hb = lays[0].h_chunk * 32
+    for v in range(3):
+        owner = vector_owner(v, world)
+        for dst in range(world):
+            if dst != owner:
+                V[dst][v][dst * hb:(dst + 1) * hb].copy_(V[owner][v][dst * hb:(dst + 1) * hb])
+    sync_all()
+    for s in shards:
+        s.witness_msms()
+    for s in shards:
+        s.h_msm()
+    parts = [s.finish() for s in shards]
+    return [s.assemble(parts, wtns=wtns, rk=rk) for s in (shards[0], shards[-1])]
 
 
 def partial_size(group):
@@ -161,6 +294,70 @@ class ShardedProver:
         if rc:
             raise ProverError(rc, _msg(e))
         return proof.raw.split(b"\0", 1)[0].decode(), public.raw.split(b"\0", 1)[0].decode()
+
+    # ---- phase-by-phase protocol (ugb_shard_*, include/ultragroth_b200.h): nothing replicated that does not have to be ----
+    def layout(self):
+        lay = ShardLayout()
+        check(lib().ugb_shard_layout_get(self.handle, ctypes.byref(lay)))
+        return lay
+
+    def _phase(self, name, *args):
+        from .prover import _err, _msg, ProverError
+        e = _err()
+        rc = getattr(lib(), name)(self.handle, *args, e, ctypes.c_ulonglong(self.ERR - 1))
+        if rc:
+            raise ProverError(rc, _msg(e))
+
+    def upload_slice(self, wtns):
+        from .prover import _buf
+        p, n, keep = _buf(wtns)
+        self._phase("ugb_shard_upload_slice", p, ctypes.c_ulonglong(n))
+
+    def round_partial_resident(self) -> bytes:
+        out = ctypes.create_string_buffer(128)
+        self._phase("ugb_shard_round_partial", out)
+        return out.raw
+
+    def lookup(self, round_partials, rk):
+        self._phase("ugb_shard_lookup", b"".join(round_partials), ctypes.c_uint32(len(round_partials)), int(rk).to_bytes(32, "little"))
+
+    def h_transform(self, mask):
+        self._phase("ugb_shard_h_transform", ctypes.c_int(mask))
+
+    def witness_msms(self):
+        self._phase("ugb_shard_witness_msms")
+
+    def h_msm(self):
+        self._phase("ugb_shard_h_msm")
+
+    def finish(self) -> bytes:
+        out = ctypes.create_string_buffer(self.partial_size)
+        self._phase("ugb_shard_finish", out)
+        return out.raw
+
+    def prove2(self, wtns, rk=None, comm=None):
+        """Collective, phase by phase: this rank uploads only its witness slice, the slices are all-gathered between the GPUs, the three
+        H-pipeline transforms run on up to three ranks and each rank receives its point range of a', b', c' (see DistComm).  Every rank
+        passes the same witness file (only rank `root` reads the public signals from it) and, for UltraGroth, the same r_k."""
+        comm = comm or DistComm(self)
+        with comm.stream_scope():
+            self.upload_slice(wtns)
+            comm.all_gather_witness()
+            if self.ultra:
+                if rk is None:
+                    raise ValueError("sharded UltraGroth proving needs a common r_k (draw it once and broadcast it)")
+                rounds = self.exchange(self.round_partial_resident())
+                self.lookup(rounds, rk)
+            self.h_transform(vector_mask(self.rank, self.world))
+            pending = comm.scatter_vectors()
+            self.witness_msms()
+            comm.wait(pending)
+            self.h_msm()
+            mine = self.finish()
+        parts = self.exchange(mine)
+        if self.root is not None and self.rank != self.root:
+            return None
+        return self.assemble(parts, wtns=wtns, rk=rk)
 
     def prove(self, wtns, rk=None):
         """Collective: every rank calls it with the same witness (and, for UltraGroth, the same r_k < 2^248)."""
