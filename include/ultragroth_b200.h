@@ -146,6 +146,16 @@ int ugb_ultra_groth_prove_raw(void* prover_object, void* wtns_signals, const uin
                               void* out_A64, void* out_B128, void* out_final_commitment64, void* out_round_commitment64, char* error_msg,
                               unsigned long long error_msg_maxsize);
 
+/* ---- batched / pipelined proving: `count` witnesses against one resident prover ----
+ * The same outputs as `count` calls of groth16_prover_prove / ultra_groth_prover_prove (src/prover.cpp:501-579 called repeatedly on one
+ * object), but witness k+1 is uploaded on a copy stream while proof k computes and the host tail of proof k (partial-sum combine,
+ * blinding, assembly, JSON) runs while the GPU already works on proof k+1.  Witness buffers should be pinned host memory (a pageable
+ * buffer makes the upload synchronous).  proof_sizes / public_sizes: capacities in, as in include/prover.h.  Return codes as prover.h;
+ * on error no output is valid. */
+int ugb_prover_prove_batch(void* prover_object, uint32_t count, const void* const* wtns_buffers, const unsigned long long* wtns_sizes,
+                           char* const* proof_buffers, unsigned long long* proof_sizes, char* const* public_buffers, unsigned long long* public_sizes,
+                           char* error_msg, unsigned long long error_msg_maxsize);
+
 /* ---- sharded proving, phase by phase (what ultragroth_b200/sharded.py drives; SURVEY.md 8(e) both bullets) ----
  * Nothing is replicated that does not have to be: every rank uploads only ITS slice of the witness over PCIe and the slices are
  * all-gathered between the GPUs (NVLink) in place; the three transforms of the H pipeline (src/groth16.cpp:110-140) run on up to

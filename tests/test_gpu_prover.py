@@ -93,3 +93,37 @@ def test_groth16_matches_committed_golden_proof(fixture):
     # the one-shot entry point (no window tables) gives the same verdict
     pj1, uj1 = up.prove_oneshot(zk, wt, "groth16")
     assert og.groth16_verify(vk, og.proof_from_json(pj1), [int(x) for x in json.loads(uj1)])
+
+
+@pytest.mark.parametrize("protocol", ["groth16", "ultragroth"])
+def test_pipelined_batch_equals_sequential_proofs(ctx, protocol):
+    """ugb_prover_prove_batch (N3): witness k+1 uploads on a copy stream into the second witness buffer while proof k computes and the
+    host tail of proof k is deferred behind proof k+1 -- with fixed blinding every proof must equal the one *_prover_prove gives
+    for the same witness.  The witnesses differ from each other (a few perturbed signals: the prover does not check satisfiability,
+    the proof points are still a deterministic function of the witness), so a buffer mix-up cannot go unnoticed."""
+    ultra = protocol == "ultragroth"
+    if ultra:
+        zk, wt, _ = ctx.synth(11, seed=555, ultra=True, lookup_bits=5, n_chunks=400)
+    else:
+        zk, wt, _ = ctx.synth(11, seed=556)
+    zk, wt = zk.tobytes(), wt.tobytes()
+    from oracle import formats as fm
+    off2 = fm.BinFile(wt, "wtns", 2).sections[2][0][0]
+    variants = []
+    for k in range(5):
+        b = bytearray(wt)
+        for sig in (7 + k, 100 + 3 * k, 900):
+            b[off2 + 32 * sig:off2 + 32 * sig + 8] = (0x1234567 * (k + 1) + sig).to_bytes(8, "little")
+        variants.append(bytes(b))
+    p = up.Prover(zk, protocol)
+    p.set_blinding(1111, 2222, 3333)
+    want = [p.prove(w) for w in variants]
+    assert len({w[0] for w in want}) == len(variants)
+    got = up.prove_batch(p, variants)
+    assert got == want
+    # and again on the same object (buffers are left in a consistent state), odd count, then a plain call
+    assert up.prove_batch(p, variants[:3]) == want[:3]
+    assert p.prove(variants[4]) == want[4]
+    assert p.prove_resident() == want[4]
+    assert up.prove_batch(p, []) == []
+    p.close()

@@ -63,6 +63,7 @@ def _declare(L):
     L.ugb_prover_last_msms.argtypes = [vp, vp]
     L.ugb_prover_last_witness.argtypes = [vp, vp, u64, u64]
     L.ugb_prover_create_times.argtypes = [vp, c.POINTER(c.c_double)]
+    L.ugb_prover_prove_batch.argtypes = [vp, c.c_uint32, vp, vp, vp, vp, vp, vp, vp, c.c_ulonglong]
     L.ugb_prover_inf_points.argtypes = [vp, c.POINTER(u64)]
     L.ugb_prover_last_proof.argtypes = [vp, vp, u64, vp, u64]
     L.ugb_prover_set_timing.argtypes = [vp, i32]

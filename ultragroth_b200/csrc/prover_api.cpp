@@ -7,6 +7,7 @@
 #include "../../include/prover.h"
 #include "../../include/ultragroth_b200.h"
 
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -32,6 +33,16 @@ public:
 class InvalidWitnessLengthException : public std::invalid_argument {
 public:
     explicit InvalidWitnessLengthException(const std::string& msg) : std::invalid_argument(msg) {}
+};
+
+// UGB_BATCH_TRACE=1: host timestamps (ms since the batch began) at the seams of the pipelined batch, to stderr
+struct BatchTrace {
+    bool on = getenv("UGB_BATCH_TRACE") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    void at(uint32_t k, const char* what) {
+        if (!on) return;
+        fprintf(stderr, "[batch] proof %u %-18s %8.3f ms\n", k, what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    }
 };
 
 void CopyError(char* error_msg, unsigned long long maxsize, const char* str) {
@@ -306,6 +317,39 @@ public:
         dev->prove_groth16(w, m);
         finish(m, w, stringProof, stringPublic);
     }
+    // `count` proofs, pipelined (N3): witness k+1 is uploaded on a copy stream while proof k computes, and the host tail of proof k
+    // (partial-sum Horner, blinding, assembly, JSON) runs after proof k+1 has been enqueued.  Same results as `count` prove() calls.
+    void prove_batch(uint32_t count, const void* const* wtns_buffers, const unsigned long long* wtns_sizes, std::vector<std::string>& proofs,
+                     std::vector<std::string>& publics) {
+        std::vector<const uint8_t*> w(count);
+        for (uint32_t k = 0; k < count; k++) w[k] = check_witness(wtns_buffers[k], wtns_sizes[k]);
+        proofs.resize(count);
+        publics.resize(count);
+        if (count == 0) return;
+        dev->batch_begin();
+        dev->batch_upload(w[0], 0);
+        std::string prev_sfx;
+        for (uint32_t k = 0; k < count; k++) {
+            const int slot = k & 1;
+            dev->batch_use(slot);
+            if (k + 1 < count) dev->batch_upload(w[k + 1], slot ^ 1);
+            dev->phase_witness_msms();
+            dev->phase_h_transform(7);
+            dev->phase_h_msm(true);
+            dev->batch_release(slot);
+            const std::string sfx = dev->result_suffix();
+            if (k > 0) {
+                ProofMsms m;
+                dev->phase_finish(m, &prev_sfx);
+                finish(m, w[k - 1], proofs[k - 1], publics[k - 1]);
+            }
+            prev_sfx = sfx;
+        }
+        ProofMsms m;
+        dev->phase_finish(m, &prev_sfx);
+        finish(m, w[count - 1], proofs[count - 1], publics[count - 1]);
+        dev->batch_end();
+    }
     // a whole proof from the witness already resident in HBM (bench.py's device-resident leg): same device work and host tail
     void prove_resident(std::string& stringProof, std::string& stringPublic) {
         ProofMsms m;
@@ -360,10 +404,11 @@ public:
     }
     // commitment = (sum of the round MSM) + r_k * final_delta1 (src/ultra_groth.cpp:161-184), then the challenge,
     // the lookup fill and the final-round MSMs over this prover's point range
-    void final_msms(HG1XYZZ commit, const Scalar& rk, const Lookup* lk, HG1Affine& commit_aff, ProofMsms& m) {
+    // r_k * final_delta1: O(1) host work that does not depend on the round MSM -- computed while the GPU still runs it
+    HG1XYZZ rk_delta(const Scalar& rk) { return pt_mul(from_affine_bytes<HFq>(hdr.final_delta1), rk); }
+    void final_msms(HG1XYZZ commit, const Scalar& rk, const Lookup* lk, HG1Affine& commit_aff, ProofMsms& m, const HG1XYZZ* rkd = nullptr) {
         m.round_c = commit;  // the raw round MSM (parity tap)
-        HG1XYZZ fdelta1 = from_affine_bytes<HFq>(hdr.final_delta1);
-        pt_add(commit, pt_mul(fdelta1, rk));
+        pt_add(commit, rkd ? *rkd : rk_delta(rk));
         commit_aff = pt_to_affine(commit);
         HFr rand_mont = derive_challenge(commit_aff);  // src/ultra_groth.cpp:32-58
         if (lk) stage(*lk);
@@ -379,28 +424,40 @@ public:
         last_msms = m;
         has_last = true;
     }
-    void finish(const ProofMsms& m, const Scalar& rk, const HG1Affine& commit_aff, std::string& stringProof, std::string& stringPublic) {
+    // the public signals as they stand in HBM (the challenge sits among them, filled in by compute_lookup)
+    std::vector<uint8_t> public_signals() {
+        std::vector<uint8_t> pub((size_t)hdr.nPublic * 32);
+        if (hdr.nPublic) dev->download_witness(pub.data(), 1, hdr.nPublic);
+        return pub;
+    }
+    void finish_with_public(const ProofMsms& m, const Scalar& rk, const HG1Affine& commit_aff, const std::vector<uint8_t>& pub,
+                            std::string& stringProof, std::string& stringPublic) {
         HG1Affine A, C;
         HG2Affine B;
         finish_points(m, rk, A, B, C);
         stringProof = "{\"pi_a\":" + g1_json(A) + ",\"pi_b\":" + g2_json(B) + ",\"pi_f\":" + g1_json(C) + ",\"pi_r\":" + g1_json(commit_aff) +
                       ",\"protocol\":\"ultragroth\"}";
-        std::vector<uint8_t> pub((size_t)hdr.nPublic * 32);
-        if (hdr.nPublic) dev->download_witness(pub.data(), 1, hdr.nPublic);
         stringPublic = public_json(pub.data(), hdr.nPublic, hdr.rand_indx);
+    }
+    void finish(const ProofMsms& m, const Scalar& rk, const HG1Affine& commit_aff, std::string& stringProof, std::string& stringPublic) {
+        finish_with_public(m, rk, commit_aff, public_signals(), stringProof, stringPublic);
     }
     // UltraGroth::Prover::prove(FrElement* wtns, LookupInfo&) (src/ultra_groth.cpp:401-462): raw signals + lookup arrays in, points out.
     // wtns_out: the reference fills the lookup signals into the CALLER's witness (compute_lookup writes `signals`); when non-null the
     // same nVars*32 bytes are written back.
     void prove_raw(const uint8_t* w, const Lookup& lk, HG1Affine& A, HG2Affine& B, HG1Affine& C, HG1Affine& R, uint8_t* wtns_out) {
         // the witness copy is asynchronous; the lookup arrays follow it on the same stream
+        // the head of the witness and the round commitment first; the lookup arrays follow the round kernels on the stream (they share
+        // the host->device copy engine with the tail of the witness, which travels on the copy stream meanwhile)
         dev->ultra_upload_witness(w);
+        dev->ultra_round_launch();
         stage(lk);
-        HG1XYZZ commit;
-        dev->ultra_round_msm(commit);
         Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
+        const HG1XYZZ rkd = rk_delta(rk);
+        HG1XYZZ commit;
+        dev->ultra_round_finish(commit);
         ProofMsms m;
-        final_msms(commit, rk, nullptr, R, m);
+        final_msms(commit, rk, nullptr, R, m, &rkd);
         finish_points(m, rk, A, B, C);
         if (wtns_out) dev->download_witness(wtns_out, 0, hdr.nVars);
     }
@@ -408,25 +465,91 @@ public:
         BinFile wtns(wtns_buffer, wtns_size, "wtns", 2);
         const uint8_t* w = check_witness(wtns);
         dev->ultra_upload_witness(w);
+        dev->ultra_round_launch();
         Lookup lk;
         load_lookup(wtns, lk);
         stage(lk);
-        HG1XYZZ commit;
-        dev->ultra_round_msm(commit);
         Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
+        const HG1XYZZ rkd = rk_delta(rk);
+        HG1XYZZ commit;
+        dev->ultra_round_finish(commit);
         HG1Affine commit_aff;
         ProofMsms m;
-        final_msms(commit, rk, nullptr, commit_aff, m);
+        final_msms(commit, rk, nullptr, commit_aff, m, &rkd);
         finish(m, rk, commit_aff, stringProof, stringPublic);
+    }
+    // `count` proofs, pipelined (N3): the upload of witness k+1 runs on a copy stream under the kernels of proof k, and the host tail of
+    // proof k is worked off while the GPU already runs the round commitment of proof k+1.  Same results as `count` prove() calls.
+    void prove_batch(uint32_t count, const void* const* wtns_buffers, const unsigned long long* wtns_sizes, std::vector<std::string>& proofs,
+                     std::vector<std::string>& publics) {
+        std::vector<const uint8_t*> w(count);
+        std::vector<Lookup> lk(count);
+        for (uint32_t k = 0; k < count; k++) {
+            BinFile wtns(wtns_buffers[k], wtns_sizes[k], "wtns", 2);
+            w[k] = check_witness(wtns, lk[k]);
+        }
+        proofs.resize(count);
+        publics.resize(count);
+        if (count == 0) return;
+        BatchTrace tr;
+        dev->batch_begin();
+        dev->batch_upload(w[0], 0);
+        ProofMsms prev_m;
+        Scalar prev_rk;
+        HG1Affine prev_commit;
+        std::vector<uint8_t> prev_pub;
+        for (uint32_t k = 0; k < count; k++) {
+            const int slot = k & 1;
+            tr.at(k, "begin");
+            dev->batch_use(slot);
+            stage(lk[k]);
+            dev->ultra_round_launch();
+            // only now: the next witness shares the host->device copy engine with the lookup arrays above, which gate the round MSM
+            if (k + 1 < count) dev->batch_upload(w[k + 1], slot ^ 1);
+            tr.at(k, "round enqueued");
+            if (k > 0) {
+                // proof k-1: its MSM results were waited for at the end of the previous iteration (they must leave the pinned slots
+                // before proof k's final round is enqueued); the host tail runs here, under proof k's round commitment
+                finish_with_public(prev_m, prev_rk, prev_commit, prev_pub, proofs[k - 1], publics[k - 1]);
+            }
+            Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
+            const HG1XYZZ rkd = rk_delta(rk);
+            tr.at(k, "host tail k-1 done");
+            HG1XYZZ commit;
+            dev->ultra_round_finish(commit);
+            tr.at(k, "round result");
+            HG1Affine commit_aff;
+            ProofMsms m;
+            m.round_c = commit;
+            pt_add(commit, rkd);
+            commit_aff = pt_to_affine(commit);
+            dev->ultra_lookup_apply(derive_challenge(commit_aff));
+            dev->phase_witness_msms();
+            dev->phase_h_transform(7);
+            dev->phase_h_msm(true);
+            dev->batch_release(slot);
+            tr.at(k, "final enqueued");
+            const HG1XYZZ raw_round = m.round_c;
+            dev->phase_finish(m);
+            m.round_c = raw_round;
+            tr.at(k, "msm results");
+            prev_m = m; prev_rk = rk; prev_commit = commit_aff;
+            prev_pub = public_signals();  // before the next proof switches witness buffers
+            if (k + 1 == count) finish_with_public(m, rk, commit_aff, prev_pub, proofs[k], publics[k]);
+        }
+        tr.at(count, "end");
+        dev->batch_end();
     }
     // a whole proof (both rounds, challenge, lookup fill, assembly) from the witness and lookup arrays left in HBM by the previous proof
     void prove_resident(std::string& stringProof, std::string& stringPublic) {
-        HG1XYZZ commit;
-        dev->ultra_round_msm(commit);
+        dev->ultra_round_launch();
         Scalar rk = blinding.fixed ? blinding.rk : random_blinding();
+        const HG1XYZZ rkd = rk_delta(rk);
+        HG1XYZZ commit;
+        dev->ultra_round_finish(commit);
         HG1Affine commit_aff;
         ProofMsms m;
-        final_msms(commit, rk, nullptr, commit_aff, m);
+        final_msms(commit, rk, nullptr, commit_aff, m, &rkd);
         finish(m, rk, commit_aff, stringProof, stringPublic);
     }
     HG1Affine shard_commit_aff;  // sharded v2: the blinded round commitment between ugb_shard_lookup and ugb_shard_finish
@@ -916,6 +1039,34 @@ int ugb_shard_finish(void* prover_object, void* partial_out, char* error_msg, un
     if (b->is_ultra()) m.round_c = XYZZ<HFq>::from_affine(static_cast<UltraGrothProver*>(b)->shard_commit_aff);
     else m.round_c = HG1XYZZ::inf();
     memcpy(partial_out, &m, sizeof(m));
+    API_CATCH_PROVE
+}
+
+// ---- N3: `count` proofs on one prover object, pipelined; same outputs as `count` *_prover_prove calls (include/ultragroth_b200.h) ----
+int ugb_prover_prove_batch(void* prover_object, uint32_t count, const void* const* wtns_buffers, const unsigned long long* wtns_sizes,
+                           char* const* proof_buffers, unsigned long long* proof_sizes, char* const* public_buffers, unsigned long long* public_sizes,
+                           char* error_msg, unsigned long long error_msg_maxsize) {
+    API_TRY
+    if (!prover_object) throw std::invalid_argument("Null prover object");
+    if (count && (!wtns_buffers || !wtns_sizes || !proof_buffers || !proof_sizes || !public_buffers || !public_sizes)) throw std::invalid_argument("Null argument");
+    ProverBase* b = static_cast<ProverBase*>(prover_object);
+    std::lock_guard<std::mutex> guard(b->mu);
+    const unsigned long long pmin = b->is_ultra() ? ProofBufferMinSizeUltraGroth() : ProofBufferMinSize();
+    const unsigned long long umin = PublicBufferMinSize(b->is_ultra() ? (unsigned long long)b->hdr.nPublic - 1 : b->hdr.nPublic);
+    for (uint32_t k = 0; k < count; k++) {
+        if (!wtns_buffers[k]) throw std::invalid_argument("Null witness buffer");
+        if (!proof_buffers[k]) throw std::invalid_argument("Null proof buffer");
+        if (!public_buffers[k]) throw std::invalid_argument("Null public buffer");
+        CheckAndUpdateBufferSizes(pmin, &proof_sizes[k], umin, &public_sizes[k], "Minimum");
+    }
+    std::vector<std::string> proofs, publics;
+    if (b->is_ultra()) static_cast<UltraGrothProver*>(b)->prove_batch(count, wtns_buffers, wtns_sizes, proofs, publics);
+    else static_cast<Groth16Prover*>(b)->prove_batch(count, wtns_buffers, wtns_sizes, proofs, publics);
+    for (uint32_t k = 0; k < count; k++) {
+        CheckAndUpdateBufferSizes(proofs[k].length(), &proof_sizes[k], publics[k].length(), &public_sizes[k], "Required");
+        std::strncpy(proof_buffers[k], proofs[k].c_str(), proof_sizes[k]);
+        std::strncpy(public_buffers[k], publics[k].c_str(), public_sizes[k]);
+    }
     API_CATCH_PROVE
 }
 

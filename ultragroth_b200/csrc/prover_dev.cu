@@ -357,7 +357,11 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
         need(zk.idx_c2_bytes, (uint64_t)n_c2_ * 4, "final indexes");
         const uint8_t* i1 = zk.idx_c1;
         const uint8_t* i2 = zk.idx_c2;
-        for (uint32_t i = 0; i < n_c1_; i++) { uint32_t v; memcpy(&v, i1 + (size_t)i * 4, 4); if (v >= nVars) throw std::range_error("round index out of range"); }
+        for (uint32_t i = 0; i < n_c1_; i++) {
+            uint32_t v; memcpy(&v, i1 + (size_t)i * 4, 4);
+            if (v >= nVars) throw std::range_error("round index out of range");
+            round_hi_ = std::max<uint64_t>(round_hi_, (uint64_t)v + 1);
+        }
         bool unique = true;
         {
             std::vector<bool> seen(nVars, false);
@@ -479,6 +483,14 @@ void ProverDevice::release() {
     void** ptrs[] = {&long_rows_, &long_segs_, &long_partial_, &A_, &B1_, &B2_, &C_, &H_, &C1_, (void**)&idx_c1_, (void**)&idx_c2_, (void**)&row_ptr_,
                      (void**)&skip_a_, (void**)&skip_b_, (void**)&skip_c_,
                      (void**)&coef_sig_, &coef_val_, &w_, &a_, &b_, &c_};
+    if (w_alt_) {  // w_ may be on either of the two batch buffers
+        w_ = wbuf_[0];
+        cudaFree(w_alt_);
+        w_alt_ = nullptr;
+        for (int i = 0; i < 2; i++) { cudaEventDestroy(ev_up_[i]); cudaEventDestroy(ev_free_[i]); }
+    }
+    if (copy_stream_) { cudaStreamSynchronize(copy_stream_); cudaStreamDestroy(copy_stream_); copy_stream_ = nullptr; }
+    if (ev_rest_) { cudaEventDestroy(ev_rest_); ev_rest_ = nullptr; }
     for (void** p : ptrs) if (*p) { cudaFree(*p); *p = nullptr; }
     for (auto& e : ev_) if (e) cudaEventDestroy(e);
     ev_.clear();
@@ -534,24 +546,24 @@ void ProverDevice::phase_witness_msms() {
         // A, B1 and C go through together: one shared reduction tail (msm_g1_launch_batch); the stage clock is split evenly
         const void* bases[3] = {A_, B1_, C_};
         const MsmDigits* dgs[3] = {ph.dA, ph.dB, ph.dC};
-        const std::string slots[3] = {"a", "b1", "c"};
+        const std::string slots[3] = {"a" + sfx_, "b1" + sfx_, "c" + sfx_};
         msm_g1_launch_batch(ctx, bases, 3, dgs, slots);
         mark_stage(2);
         mark_stage(3);
-        msm_g2_launch(ctx, B2_, *ph.dB, "b2");
+        msm_g2_launch(ctx, B2_, *ph.dB, "b2" + sfx_);
         mark_stage(4);
     } else {
-        msm_g1_launch(ctx, A_, *ph.dA, "a");
+        msm_g1_launch(ctx, A_, *ph.dA, "a" + sfx_);
         mark_stage(2);
-        msm_g1_launch(ctx, B1_, *ph.dB, "b1");
+        msm_g1_launch(ctx, B1_, *ph.dB, "b1" + sfx_);
         mark_stage(3);
-        msm_g2_launch(ctx, B2_, *ph.dB, "b2");
+        msm_g2_launch(ctx, B2_, *ph.dB, "b2" + sfx_);
         mark_stage(4);
         if (c_in_w) {
-            msm_g1_launch(ctx, C_, *ph.dC, "c");
+            msm_g1_launch(ctx, C_, *ph.dC, "c" + sfx_);
         } else {
             msm_sort_digits(ctx, (const uint8_t*)w_, idx_c2_, n_c2_, 0, "cidx", ph.dc, pre_ ? &cfg_c2_ : nullptr);
-            msm_g1_launch(ctx, C_, ph.dc, "c");
+            msm_g1_launch(ctx, C_, ph.dc, "c" + sfx_);
         }
     }
     mark_stage(5);
@@ -597,20 +609,21 @@ void ProverDevice::phase_h_msm(bool whole_h) {
     mark_stage(9);
     msm_sort_digits(ctx, (const uint8_t*)a_ + h_lo_ * 32, nullptr, h_hi_ - h_lo_, 0, "h", ph_.dh, pre_ ? &cfg_h_ : nullptr);
     mark_stage(10);
-    msm_g1_launch(ctx, H_, ph_.dh, "h");
+    msm_g1_launch(ctx, H_, ph_.dh, "h" + sfx_);
     mark_stage(11);
 }
 
 // phase 4: wait for the partial sums and finish them on the host
-void ProverDevice::phase_finish(ProofMsms& out) {
+void ProverDevice::phase_finish(ProofMsms& out, const std::string* sfx) {
     DeviceCtx& ctx = *ctx_;
     ctx.activate();
     Phase& ph = ph_;
-    msm_g1_finish(ctx, *ph.dA, "a", &out.a);
-    msm_g1_finish(ctx, *ph.dB, "b1", &out.b1);
-    msm_g2_finish(ctx, *ph.dB, "b2", &out.b2);
-    msm_g1_finish(ctx, *ph.dC, "c", &out.c);
-    msm_g1_finish(ctx, ph.dh, "h", &out.h);
+    const std::string& x = sfx ? *sfx : sfx_;  // a pipelined batch finishes proof k-1 after proof k was enqueued (other result slots)
+    msm_g1_finish(ctx, *ph.dA, "a" + x, &out.a);
+    msm_g1_finish(ctx, *ph.dB, "b1" + x, &out.b1);
+    msm_g2_finish(ctx, *ph.dB, "b2" + x, &out.b2);
+    msm_g1_finish(ctx, *ph.dC, "c" + x, &out.c);
+    msm_g1_finish(ctx, ph.dh, "h" + x, &out.h);
     check_lookup_error();  // the flag travelled before the MSM results on the same stream
     ctx.prof_collect();
     if (timing) {
@@ -642,6 +655,48 @@ void ProverDevice::upload_witness_slice(const uint8_t* witness) {
         UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)w_ + w_lo_ * 32, witness + w_lo_ * 32, (size_t)(w_hi_ - w_lo_) * 32, cudaMemcpyHostToDevice, ctx_->stream));
 }
 
+// ---- pipelined batches: two witness buffers and a copy stream, so that the upload of witness k+1 runs under the
+// kernels of proof k; the caller (prover_api.cpp) also defers the host tail of proof k until proof k+1 has been enqueued ----
+void ProverDevice::batch_begin() {
+    ctx_->activate();
+    if (!w_alt_) {
+        w_alt_ = dev_alloc((size_t)w_chunk() * shard_world_ * 32);
+        if (!copy_stream_) UG_CUDA_CHECK(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; i++) {
+            UG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_up_[i], cudaEventDisableTiming));
+            UG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_free_[i], cudaEventDisableTiming));
+        }
+    }
+    wbuf_[0] = w_;
+    wbuf_[1] = w_alt_;
+    // both buffers are free once everything enqueued so far has run
+    for (int i = 0; i < 2; i++) UG_CUDA_CHECK(cudaEventRecord(ev_free_[i], ctx_->stream));
+}
+// host -> device copy of a whole witness into buffer `slot` on the copy stream (waits until the proof that last used it is done)
+void ProverDevice::batch_upload(const uint8_t* witness, int slot) {
+    ctx_->activate();
+    UG_CUDA_CHECK(cudaStreamWaitEvent(copy_stream_, ev_free_[slot], 0));
+    UG_CUDA_CHECK(cudaMemcpyAsync(wbuf_[slot], witness, (size_t)nVars * 32, cudaMemcpyHostToDevice, copy_stream_));
+    UG_CUDA_CHECK(cudaEventRecord(ev_up_[slot], copy_stream_));
+}
+// the proof about to be enqueued reads buffer `slot`
+void ProverDevice::batch_use(int slot) {
+    ctx_->activate();
+    UG_CUDA_CHECK(cudaStreamWaitEvent(ctx_->stream, ev_up_[slot], 0));
+    w_ = wbuf_[slot];
+    sfx_ = slot ? "#1" : "";
+}
+// every kernel that reads buffer `slot` has been enqueued
+void ProverDevice::batch_release(int slot) {
+    UG_CUDA_CHECK(cudaEventRecord(ev_free_[slot], ctx_->stream));
+}
+void ProverDevice::batch_end() {
+    ctx_->activate();
+    UG_CUDA_CHECK(cudaStreamSynchronize(copy_stream_));
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx_->stream));
+    sfx_.clear();  // w_ stays on whichever buffer holds the last witness (prove_resident reads it)
+}
+
 void ProverDevice::prove_groth16(const uint8_t* witness, ProofMsms& out) {
     DeviceCtx& ctx = *ctx_;
     ctx.activate();
@@ -657,17 +712,39 @@ void ProverDevice::prove_resident(ProofMsms& out) {
 
 void ProverDevice::ultra_upload_witness(const uint8_t* witness) {
     ctx_->activate();
-    UG_CUDA_CHECK(cudaMemcpyAsync(w_, witness, (size_t)nVars * 32, cudaMemcpyHostToDevice, ctx_->stream));
+    // the round commitment only reads the signals of the round index list (a prefix of the witness in practice): that part goes first,
+    // on the proof's stream; the rest follows on the copy stream and is awaited by the first kernel that needs it (ultra_lookup_apply),
+    // so it travels while the round MSM runs
+    const uint64_t head = std::min<uint64_t>(round_hi_, nVars);
+    if (head == 0 || head * 2 > nVars) {
+        UG_CUDA_CHECK(cudaMemcpyAsync(w_, witness, (size_t)nVars * 32, cudaMemcpyHostToDevice, ctx_->stream));
+        return;
+    }
+    if (!copy_stream_) UG_CUDA_CHECK(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+    if (!ev_rest_) UG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_rest_, cudaEventDisableTiming));
+    // the copy stream must not overwrite signals that kernels of the PREVIOUS proof on this stream may still read
+    UG_CUDA_CHECK(cudaEventRecord(ev_rest_, ctx_->stream));
+    UG_CUDA_CHECK(cudaStreamWaitEvent(copy_stream_, ev_rest_, 0));
+    UG_CUDA_CHECK(cudaMemcpyAsync(w_, witness, (size_t)head * 32, cudaMemcpyHostToDevice, ctx_->stream));
+    UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)w_ + head * 32, witness + head * 32, (size_t)(nVars - head) * 32, cudaMemcpyHostToDevice, copy_stream_));
+    UG_CUDA_CHECK(cudaEventRecord(ev_rest_, copy_stream_));
+    rest_pending_ = true;
 }
 
-void ProverDevice::ultra_round_msm(HG1XYZZ& out) {
+void ProverDevice::ultra_round_launch() {
     DeviceCtx& ctx = *ctx_;
     ctx.activate();
     // round_wtns[i] = wtns[round_indexes[i]] (src/ultra_groth.cpp:415-419) folded into the scalar fetch
-    MsmDigits d;
-    msm_sort_digits(ctx, (const uint8_t*)w_, idx_c1_ + c1_lo_, c1_hi_ - c1_lo_, 0, "round", d, pre_ ? &cfg_c1_ : nullptr);
-    msm_g1_launch(ctx, C1_, d, "round");
-    msm_g1_finish(ctx, d, "round", &out);
+    msm_sort_digits(ctx, (const uint8_t*)w_, idx_c1_ + c1_lo_, c1_hi_ - c1_lo_, 0, "round", d_round_, pre_ ? &cfg_c1_ : nullptr);
+    msm_g1_launch(ctx, C1_, d_round_, "round");
+}
+void ProverDevice::ultra_round_finish(HG1XYZZ& out) {
+    ctx_->activate();
+    msm_g1_finish(*ctx_, d_round_, "round", &out);
+}
+void ProverDevice::ultra_round_msm(HG1XYZZ& out) {
+    ultra_round_launch();
+    ultra_round_finish(out);
 }
 
 void ProverDevice::ultra_lookup_stage(const void* chunks, uint32_t chunks_len, const void* freqs, uint32_t freqs_len,
@@ -692,6 +769,10 @@ void ProverDevice::ultra_lookup_stage(const void* chunks, uint32_t chunks_len, c
 void ProverDevice::ultra_lookup_apply(const HFr& rand_mont) {
     DeviceCtx& ctx = *ctx_;
     ctx.activate();
+    if (rest_pending_) {  // the tail of the witness (ultra_upload_witness) must have landed before anything reads or fills it
+        UG_CUDA_CHECK(cudaStreamWaitEvent(ctx.stream, ev_rest_, 0));
+        rest_pending_ = false;
+    }
     const uint32_t chunks_len = lk_chunks_len_, freqs_len = lk_freqs_len_, idx_len = lk_idx_len_;
     uint32_t* d_chunks = (uint32_t*)ctx.workspace("lk.chunks", (size_t)chunks_len * 4 + 16);
     uint32_t* d_freqs = (uint32_t*)ctx.workspace("lk.freqs", (size_t)freqs_len * 4 + 16);

@@ -72,7 +72,14 @@ public:
     void phase_witness_msms();
     void phase_h_transform(int mask);
     void phase_h_msm(bool whole_h);
-    void phase_finish(ProofMsms& out);
+    void phase_finish(ProofMsms& out, const std::string* sfx = nullptr);
+    // pipelined batches (N3): see prover_dev.cu
+    void batch_begin();
+    void batch_upload(const uint8_t* witness, int slot);
+    void batch_use(int slot);
+    void batch_release(int slot);
+    void batch_end();
+    std::string result_suffix() const { return sfx_; }
     ~ProverDevice();
     double create_ms[4] = {0, 0, 0, 0};  // create-time breakdown: base uploads, coefficient CSR, window tables, total
 
@@ -89,6 +96,8 @@ public:
     // ---- UltraGroth (src/ultra_groth.cpp:401-462) ----
     void ultra_upload_witness(const uint8_t* witness);
     void ultra_round_msm(HG1XYZZ& out);                                   // execute_round's MSM (:168)
+    void ultra_round_launch();                                            // ... enqueued only / host half
+    void ultra_round_finish(HG1XYZZ& out);
     // compute_lookup (:62-106) in two halves: _stage copies the four u32 index arrays to HBM (asynchronous; the host arrays -- any
     // alignment -- must stay valid until the proof's final synchronisation), _apply runs the kernels once the challenge is known;
     // indices are range-checked on the device and a violation surfaces as std::range_error from ultra_final_msms
@@ -113,6 +122,14 @@ private:
         bool batched = false;
     } ph_;
     uint32_t shard_rank_ = 0, shard_world_ = 1;
+    MsmDigits d_round_;
+    std::string sfx_;  // suffix of the pinned MSM result slots of the proof being enqueued ("" / "#1": two proofs can be in flight)
+    void *w_alt_ = nullptr, *wbuf_[2] = {nullptr, nullptr};
+    cudaStream_t copy_stream_ = nullptr;
+    cudaEvent_t ev_rest_ = nullptr;   // tail of a split witness upload (ultra_upload_witness)
+    bool rest_pending_ = false;
+    uint64_t round_hi_ = 0;           // 1 + the largest signal index the round commitment reads
+    cudaEvent_t ev_up_[2] = {nullptr, nullptr}, ev_free_[2] = {nullptr, nullptr};
     void mark_stage(int idx);
     void construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t shard_world, bool tables);
     void release();

@@ -184,6 +184,25 @@ class Prover:
         return proof.raw.split(b"\0", 1)[0].decode(), public.raw.split(b"\0", 1)[0].decode()
 
 
+def prove_batch(prover, wtns_list):
+    """ugb_prover_prove_batch: pipelined proofs of several witnesses on one resident prover -> [(proof_json, public_json)]"""
+    n = len(wtns_list)
+    bufs = [_buf(w) for w in wtns_list]
+    wp = (ctypes.c_void_p * n)(*[b[0] for b in bufs])
+    ws = (ctypes.c_ulonglong * n)(*[b[1] for b in bufs])
+    proofs = [ctypes.create_string_buffer(prover.proof_size + 1) for _ in range(n)]
+    publics = [ctypes.create_string_buffer(prover.public_size + 1) for _ in range(n)]
+    pp = (ctypes.c_char_p * n)(*[ctypes.cast(p, ctypes.c_char_p) for p in proofs])
+    up_ = (ctypes.c_char_p * n)(*[ctypes.cast(p, ctypes.c_char_p) for p in publics])
+    ps = (ctypes.c_ulonglong * n)(*([prover.proof_size] * n))
+    us = (ctypes.c_ulonglong * n)(*([prover.public_size] * n))
+    e = _err()
+    rc = lib().ugb_prover_prove_batch(prover.handle, n, wp, ws, pp, ps, up_, us, e, ERR_SIZE - 1)
+    if rc:
+        raise ProverError(rc, _msg(e))
+    return [(p.raw.split(b"\0", 1)[0].decode(), u.raw.split(b"\0", 1)[0].decode()) for p, u in zip(proofs, publics)]
+
+
 def prove_oneshot(zkey, wtns, protocol="groth16"):
     """groth16_prover / ultra_groth_prover (create + prove + destroy)."""
     pre = _prefix(protocol)
