@@ -196,6 +196,24 @@ void ntt_run(DeviceCtx& ctx, NttTables& tabs, Fr* const* d_vecs, int count, int 
         dim3 grid(tiles, count);
         const char* kname = dif ? (ps.lo ? "k_ntt_pass<dif,strided>" : "k_ntt_pass<dif,contig>")
                                 : (ps.lo ? "k_ntt_pass<dit,strided>" : "k_ntt_pass<dit,contig>");
+        // opt-in TMA variant of the contiguous pass (UGB_NTT_TMA=1): persistent CTAs, bulk copies in and out, mbarrier completion
+        static const int use_tma = env_int("UGB_NTT_TMA", 0);
+        if (use_tma && ps.lo == 0 && ps.logC == 0 && ps.T >= 6) {
+            if (!ctx.flag("ntt.bulk_optin")) {
+                UG_CUDA_CHECK(cudaFuncSetAttribute(k_ntt_pass_bulk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                UG_CUDA_CHECK(cudaFuncSetAttribute(k_ntt_pass_bulk<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                ctx.set_flag("ntt.bulk_optin");
+            }
+            const uint32_t total = tiles * (uint32_t)count;
+            const size_t bsmem = 2 * (size_t)E * 32 + 64;
+            const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(4, (200 * 1024) / bsmem));
+            const int bthreads = std::min(1024, std::max(128, env_int("UGB_NTT_TMA_THREADS", (int)std::min<uint32_t>(512, E / 4))));
+            const uint32_t bgrid = std::min<uint32_t>(total, (uint32_t)(ctx.sm_count * per_sm));
+            const char* bname = dif ? "k_ntt_pass_bulk<dif>" : "k_ntt_pass_bulk<dit>";
+            if (dif) UG_KERNEL(ctx, bname, k_ntt_pass_bulk<true><<<bgrid, bthreads, bsmem, ctx.stream>>>(a, tiles, total));
+            else UG_KERNEL(ctx, bname, k_ntt_pass_bulk<false><<<bgrid, bthreads, bsmem, ctx.stream>>>(a, tiles, total));
+            continue;
+        }
         if (dif) UG_KERNEL(ctx, kname, k_ntt_pass<true><<<grid, bt, smem, ctx.stream>>>(a));
         else UG_KERNEL(ctx, kname, k_ntt_pass<false><<<grid, bt, smem, ctx.stream>>>(a));
     }
