@@ -67,14 +67,20 @@ static void exclusive_scan_u32(DeviceCtx& ctx, const uint32_t* in, uint32_t n, u
     UG_KERNEL(ctx, "k_scan_apply", k_scan_apply<<<ntiles, SCAN_BS, 0, ctx.stream>>>(in, n, tiles, out));
 }
 
+void msm_inf_bitmap_async(DeviceCtx& ctx, int group, const void* d_bases, uint64_t n, uint32_t* d_bitmap, bool combine, uint32_t* d_count) {
+    ctx.activate();
+    if (n == 0) return;
+    const int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx.sm_count * 8);
+    if (group == 1) UG_KERNEL(ctx, "k_inf_bitmap", k_inf_bitmap<Fq><<<blocks, 256, 0, ctx.stream>>>((const G1Affine*)d_bases, (uint32_t)n, d_bitmap, combine ? 1 : 0, d_count));
+    else UG_KERNEL(ctx, "k_inf_bitmap", k_inf_bitmap<Fq2c><<<blocks, 256, 0, ctx.stream>>>((const Affine<Fq2c>*)d_bases, (uint32_t)n, d_bitmap, combine ? 1 : 0, d_count));
+}
+
 uint64_t msm_inf_bitmap(DeviceCtx& ctx, int group, const void* d_bases, uint64_t n, uint32_t* d_bitmap, bool combine) {
     ctx.activate();
     if (n == 0) return 0;
     uint32_t* d_count = (uint32_t*)ctx.workspace("msm.inf_count", 16);
     UG_CUDA_CHECK(cudaMemsetAsync(d_count, 0, 4, ctx.stream));
-    const int blocks = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx.sm_count * 8);
-    if (group == 1) UG_KERNEL(ctx, "k_inf_bitmap", k_inf_bitmap<Fq><<<blocks, 256, 0, ctx.stream>>>((const G1Affine*)d_bases, (uint32_t)n, d_bitmap, combine ? 1 : 0, d_count));
-    else UG_KERNEL(ctx, "k_inf_bitmap", k_inf_bitmap<Fq2c><<<blocks, 256, 0, ctx.stream>>>((const Affine<Fq2c>*)d_bases, (uint32_t)n, d_bitmap, combine ? 1 : 0, d_count));
+    msm_inf_bitmap_async(ctx, group, d_bases, n, d_bitmap, combine, d_count);
     uint32_t h = 0;
     UG_CUDA_CHECK(cudaMemcpyAsync(&h, d_count, 4, cudaMemcpyDeviceToHost, ctx.stream));
     UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
@@ -305,14 +311,14 @@ static void* build_table_impl(DeviceCtx& ctx, const Affine<F>* d_bases, uint64_t
     UG_CUDA_CHECK(cudaMalloc((void**)&table, std::max<size_t>(level_bytes * cfg.W, 16)));
     if (n == 0) return table;
     UG_CUDA_CHECK(cudaMemcpyAsync(table, d_bases, level_bytes, cudaMemcpyDeviceToDevice, ctx.stream));
-    XYZZ<F>* tmp = (XYZZ<F>*)ctx.workspace("msm.table_tmp", (size_t)n * sizeof(XYZZ<F>));
+    Jac<F>* tmp = (Jac<F>*)ctx.workspace("msm.table_tmp", (size_t)n * sizeof(Jac<F>));
     const int blocks = (int)std::min<uint64_t>((n + 127) / 128, (uint64_t)ctx.sm_count * 8);
     const int blocks_aff = (int)std::min<uint64_t>((n + 128 * AFF_RUN - 1) / (128 * AFF_RUN), (uint64_t)ctx.sm_count * 8);
     for (int w = 1; w < cfg.W; w++) {
         UG_KERNEL(ctx, "k_table_shift", k_table_shift<F><<<blocks, 128, 0, ctx.stream>>>(table + (size_t)(w - 1) * n, (uint32_t)n, cfg.c, tmp));
         UG_KERNEL(ctx, "k_batch_to_affine", k_batch_to_affine<F><<<std::max(blocks_aff, 1), 128, 0, ctx.stream>>>(tmp, (uint32_t)n, table + (size_t)w * n));
     }
-    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+    // no synchronisation: the caller overlaps the next array's upload with these kernels (everything is in stream order)
     return table;
 }
 

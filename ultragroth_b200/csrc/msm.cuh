@@ -668,21 +668,21 @@ __global__ void __launch_bounds__(SUM_BS) k_bit_sums(const XYZZ<F>* __restrict__
 // level k of the table holds 2^(c*k) * P_i in affine form.  k_table_shift: out = 2^c * in (XYZZ, no inversion);
 // k_batch_to_affine: RUN points per thread share one field inversion (Montgomery's trick).
 template <class F>
-__global__ void __launch_bounds__(128) k_table_shift(const Affine<F>* __restrict__ in, uint32_t n, int c, XYZZ<F>* __restrict__ out) {
+__global__ void __launch_bounds__(128) k_table_shift(const Affine<F>* __restrict__ in, uint32_t n, int c, Jac<F>* __restrict__ out) {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         Affine<F> a = ld_nc(&in[i]);
-        XYZZ<F> p = pt_dbl_affine(a);
-        for (int k = 1; k < c; k++) p = pt_dbl(p);
+        Jac<F> p = jac_dbl_affine(a);
+        for (int k = 1; k < c; k++) p = jac_dbl(p);
         st_g(&out[i], p);
     }
 }
 
 constexpr int AFF_RUN = 8;
 template <class F>
-__global__ void __launch_bounds__(128) k_batch_to_affine(const XYZZ<F>* __restrict__ in, uint32_t n, Affine<F>* __restrict__ out) {
+__global__ void __launch_bounds__(128) k_batch_to_affine(const Jac<F>* __restrict__ in, uint32_t n, Affine<F>* __restrict__ out) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t T = gridDim.x * blockDim.x;
-    // thread t owns points t, t+T, t+2T, ... (coalesced), AFF_RUN at a time
+    // thread t owns points t, t+T, t+2T, ... (coalesced), AFF_RUN at a time: one field inversion per run (Montgomery's trick)
     for (uint32_t base = t; base < n; base += T * AFF_RUN) {
         F pre[AFF_RUN];
         F acc = F::one();
@@ -691,7 +691,7 @@ __global__ void __launch_bounds__(128) k_batch_to_affine(const XYZZ<F>* __restri
             const uint32_t i = base + k * T;
             pre[k] = acc;
             if (i < n) {
-                F z = ld_g(&in[i].ZZZ);
+                F z = ld_g(&in[i].Z);
                 if (!z.is_zero()) acc = fmul(acc, z);
             }
         }
@@ -700,14 +700,14 @@ __global__ void __launch_bounds__(128) k_batch_to_affine(const XYZZ<F>* __restri
         for (int k = AFF_RUN - 1; k >= 0; k--) {
             const uint32_t i = base + k * T;
             if (i >= n) continue;
-            XYZZ<F> p = ld_g(&in[i]);
+            Jac<F> p = ld_g(&in[i]);
             Affine<F> a = Affine<F>::inf();
-            if (!p.ZZZ.is_zero()) {
-                F izzz = fmul(inv, pre[k]);
-                inv = fmul(inv, p.ZZZ);
-                F izz = fsqr(fmul(izzz, p.ZZ));  // (ZZ/ZZZ)^2 = 1/ZZ
-                a.x = fmul(p.X, izz);
-                a.y = fmul(p.Y, izzz);
+            if (!p.Z.is_zero()) {
+                F zi = fmul(inv, pre[k]);
+                inv = fmul(inv, p.Z);
+                F zi2 = fsqr(zi);
+                a.x = fmul(p.X, zi2);
+                a.y = fmul(p.Y, fmul(zi2, zi));
             }
             st_g(&out[i], a);
         }

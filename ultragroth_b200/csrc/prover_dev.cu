@@ -330,9 +330,77 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
     });
     struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } joiner{csr_thread};
 
-    A_ = upload(ctx, zk.A + w_lo_ * 64, (size_t)wn * 64);
-    B1_ = upload(ctx, zk.B1 + w_lo_ * 64, (size_t)wn * 64);
-    B2_ = upload(ctx, zk.B2 + w_lo_ * 128, (size_t)wn * 128);
+    // ---- bases: upload, zero-point maps, window tables -- pipelined ----
+    // Uploads go on their own stream (the zkey buffer is pageable host memory: every copy blocks THIS thread while it is staged, but
+    // not the GPU), and the table of an array is built on the compute stream as soon as its upload has landed: the GPU builds the table
+    // of array i while the host pushes array i+1.  Nothing is synchronised or freed until the end (cudaFree would drain the device).
+    cudaStream_t up = nullptr;
+    UG_CUDA_CHECK(cudaStreamCreateWithFlags(&up, cudaStreamNonBlocking));
+    std::vector<cudaEvent_t> up_events;
+    std::vector<void*> garbage;  // level-0 base arrays superseded by their tables, scratch copies
+    struct Cleanup {
+        cudaStream_t& up; std::vector<cudaEvent_t>& ev; std::vector<void*>& g; DeviceCtx& ctx;
+        ~Cleanup() {
+            cudaStreamSynchronize(up); cudaStreamSynchronize(ctx.stream);
+            for (auto e : ev) cudaEventDestroy(e);
+            for (void* p : g) cudaFree(p);
+            cudaStreamDestroy(up);
+        }
+    } cleanup{up, up_events, garbage, ctx};
+    auto upload_up = [&](const void* src, size_t bytes) -> void* {
+        void* p = dev_alloc(bytes);
+        if (bytes) UG_CUDA_CHECK(cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, up));
+        return p;
+    };
+    auto landed = [&]() {  // the compute stream waits for everything pushed on the upload stream so far
+        cudaEvent_t e;
+        UG_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        up_events.push_back(e);
+        UG_CUDA_CHECK(cudaEventRecord(e, up));
+        UG_CUDA_CHECK(cudaStreamWaitEvent(ctx.stream, e, 0));
+    };
+    const char* pre_env = getenv("UGB_MSM_PRE");
+    pre_ = tables && !(pre_env && atoi(pre_env) == 0);
+    double t_tables = 0;
+    auto tabulate = [&](void*& base, int group, uint64_t count, MsmConfig& cfg) {
+        if (!pre_) return;
+        const double t0 = now_ms();
+        MsmTable t = msm_build_table(ctx, group, base, count);  // enqueued, not waited for
+        garbage.push_back(base);
+        base = t.d_table;
+        cfg = t.cfg;
+        t_tables += now_ms() - t0;
+    };
+    // zero-point maps: which witness-paired bases are the point at infinity (their polynomial vanishes at tau: signals that never
+    // occur in that matrix).  A class with enough of them gets its own digit sort without those points: an infinity base costs its
+    // lane a whole idle mixed addition in k_accumulate, a skipped digit costs nothing.  G1-only classes need >= 15 % to repay the
+    // extra sort, the class holding the G2 array >= 4 %.  The counts are read back at the very end.
+    const size_t bm_words = (size_t)((wn + 31) / 32) * 4 + 16;
+    uint32_t* d_counts = (uint32_t*)dev_alloc(64);
+    garbage.push_back(d_counts);
+    UG_CUDA_CHECK(cudaMemsetAsync(d_counts, 0, 64, ctx.stream));
+    uint32_t *bm_a = nullptr, *bm_b = nullptr, *bm_c = nullptr;
+    auto bitmap = [&](uint32_t*& bm, int slot, int group, const void* bases, bool combine) {
+        if (wn == 0) return;
+        if (!bm) bm = (uint32_t*)dev_alloc(bm_words);
+        if (combine) UG_CUDA_CHECK(cudaMemsetAsync(d_counts + slot, 0, 4, ctx.stream));
+        msm_inf_bitmap_async(ctx, group, bases, wn, bm, combine, d_counts + slot);
+    };
+    MsmConfig tmp;
+    if (pre_) ctx.workspace("msm.table_tmp", std::max<uint64_t>(wn, hn) * sizeof(Jac<Fq2c>) + 256);  // sized once: growing it later would drain the stream
+
+    A_ = upload_up(zk.A + w_lo_ * 64, (size_t)wn * 64);
+    landed();
+    bitmap(bm_a, 0, 1, A_, false);
+    tabulate(A_, 1, wn, cfg_w_);
+    B1_ = upload_up(zk.B1 + w_lo_ * 64, (size_t)wn * 64);
+    landed();
+    bitmap(bm_b, 1, 1, B1_, false);
+    tabulate(B1_, 1, wn, tmp);
+    B2_ = upload_up(zk.B2 + w_lo_ * 128, (size_t)wn * 128);
+    landed();
+    bitmap(bm_b, 1, 2, B2_, true);
+    tabulate(B2_, 2, wn, tmp);
     if (!ultra_) {
         const uint32_t nc = nVars - nPublic - 1;
         need(zk.C_bytes, (uint64_t)nc * 64, "pointsC");
@@ -340,14 +408,16 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
         // C MSM reuses the sorted digits of the full witness
         // slot i of the padded array = pointsC[i - (nPublic+1)] for i > nPublic, infinity below; keep [w_lo_, w_hi_)
         C_ = dev_alloc((size_t)wn * 64);
-        UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, std::max<size_t>((size_t)wn * 64, 16), ctx.stream));
+        UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, std::max<size_t>((size_t)wn * 64, 16), up));
         {
             const uint64_t first = std::max<uint64_t>(w_lo_, (uint64_t)nPublic + 1);
             if (first < w_hi_)
-                UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)C_ + (first - w_lo_) * 64, zk.C + (first - nPublic - 1) * 64, (size_t)(w_hi_ - first) * 64, cudaMemcpyHostToDevice, ctx.stream));
+                UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)C_ + (first - w_lo_) * 64, zk.C + (first - nPublic - 1) * 64, (size_t)(w_hi_ - first) * 64, cudaMemcpyHostToDevice, up));
         }
         c_shares_witness_sort_ = true;
-        H_ = upload(ctx, zk.H + h_lo_ * 64, (size_t)hn * 64);
+        landed();
+        bitmap(bm_c, 2, 1, C_, false);
+        tabulate(C_, 1, wn, tmp);
     } else {
         n_c1_ = zk.n_c1;
         n_c2_ = zk.n_c2;
@@ -373,74 +443,38 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
             }
         }
         shard_range(n_c1_, shard_world, shard_rank, c1_lo_, c1_hi_);
-        C1_ = upload(ctx, zk.C1 + c1_lo_ * 64, (size_t)(c1_hi_ - c1_lo_) * 64);
-        idx_c1_ = (uint32_t*)upload(ctx, zk.idx_c1, (size_t)n_c1_ * 4);
-        idx_c2_ = (uint32_t*)upload(ctx, zk.idx_c2, (size_t)n_c2_ * 4);
+        idx_c1_ = (uint32_t*)upload_up(zk.idx_c1, (size_t)n_c1_ * 4);
+        idx_c2_ = (uint32_t*)upload_up(zk.idx_c2, (size_t)n_c2_ * 4);
         if (unique) {
             // final_wtns[i] = wtns[final_idx[i]] (src/ultra_groth.cpp:439-445): place C2[i] at slot final_idx[i]
             // of an nVars-long array of points at infinity, so the final C MSM shares the witness digits (scatter on the device)
-            void* c2 = upload(ctx, zk.C, (size_t)n_c2_ * 64);
+            void* c2 = upload_up(zk.C, (size_t)n_c2_ * 64);
+            garbage.push_back(c2);
             C_ = dev_alloc((size_t)wn * 64);
+            landed();
             UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, std::max<size_t>((size_t)wn * 64, 16), ctx.stream));
             if (n_c2_) {
                 const int blocks = (int)std::min<uint64_t>(((uint64_t)n_c2_ + 255) / 256, (uint64_t)ctx.sm_count * 8);
                 UG_KERNEL(ctx, "k_scatter_affine", k_scatter_affine<<<blocks, 256, 0, ctx.stream>>>((const G1Affine*)c2, idx_c2_, n_c2_, (uint32_t)w_lo_, (uint32_t)w_hi_, (G1Affine*)C_));
             }
-            UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
-            UG_CUDA_CHECK(cudaFree(c2));
             c_shares_witness_sort_ = true;
+            bitmap(bm_c, 2, 1, C_, false);
+            tabulate(C_, 1, wn, tmp);
         } else {
             if (shard_world > 1) throw std::invalid_argument("sharded UltraGroth prover needs unique final-round indexes");
-            C_ = upload(ctx, zk.C, (size_t)n_c2_ * 64);
+            C_ = upload_up(zk.C, (size_t)n_c2_ * 64);
             c_shares_witness_sort_ = false;
+            landed();
+            tabulate(C_, 1, n_c2_, cfg_c2_);
         }
-        H_ = upload(ctx, zk.H + h_lo_ * 64, (size_t)hn * 64);
+        C1_ = upload_up(zk.C1 + c1_lo_ * 64, (size_t)(c1_hi_ - c1_lo_) * 64);
+        landed();
+        tabulate(C1_, 1, c1_hi_ - c1_lo_, cfg_c1_);
     }
-    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
-    // zero-point maps: which witness-paired bases are the point at infinity (their polynomial vanishes at tau: signals that never
-    // occur in that matrix).  A class with enough of them gets its own digit sort without those points: an infinity base costs its
-    // lane a whole idle mixed addition in k_accumulate, a skipped digit costs nothing.  G1-only classes need >= 15 % to repay the
-    // extra sort, the class holding the G2 array >= 4 %.
-    {
-        const char* e = getenv("UGB_MSM_SKIP_INF");
-        const bool enabled = !(e && atoi(e) == 0) && wn > 0;
-        const size_t words = (size_t)((wn + 31) / 32) * 4 + 16;
-        auto classify = [&](uint32_t*& skip, uint64_t& count, const void* g1a, const void* g2a, double thr) {
-            uint32_t* bm = (uint32_t*)dev_alloc(words);
-            count = msm_inf_bitmap(ctx, 1, g1a, wn, bm, false);
-            if (g2a) count = msm_inf_bitmap(ctx, 2, g2a, wn, bm, true);
-            if (enabled && (double)count >= thr * (double)wn) skip = bm;
-            else UG_CUDA_CHECK(cudaFree(bm));
-        };
-        classify(skip_a_, inf_points[0], A_, nullptr, 0.15);
-        classify(skip_b_, inf_points[1], B1_, B2_, 0.04);
-        if (c_shares_witness_sort_) classify(skip_c_, inf_points[2], C_, nullptr, 0.15);
-    }
-    create_ms[0] = now_ms() - t_begin;
-
-    // window tables: 2^(c*w) multiples of every base, resident next to the bases they replace (UGB_MSM_PRE=0: off)
-    {
-        const double t0 = now_ms();
-        const char* e = getenv("UGB_MSM_PRE");
-        pre_ = tables && !(e && atoi(e) == 0);
-        if (pre_) {
-            auto tabulate = [&](void*& base, int group, uint64_t count, MsmConfig& cfg) {
-                MsmTable t = msm_build_table(ctx, group, base, count);
-                UG_CUDA_CHECK(cudaFree(base));
-                base = t.d_table;
-                cfg = t.cfg;
-            };
-            MsmConfig tmp;
-            tabulate(A_, 1, wn, cfg_w_);
-            tabulate(B1_, 1, wn, tmp);
-            tabulate(B2_, 2, wn, tmp);
-            if (c_shares_witness_sort_) tabulate(C_, 1, wn, tmp);
-            else tabulate(C_, 1, n_c2_, cfg_c2_);
-            tabulate(H_, 1, hn, cfg_h_);
-            if (ultra_) tabulate(C1_, 1, c1_hi_ - c1_lo_, cfg_c1_);
-        }
-        create_ms[2] = now_ms() - t0;
-    }
+    H_ = upload_up(zk.H + h_lo_ * 64, (size_t)hn * 64);
+    landed();
+    tabulate(H_, 1, hn, cfg_h_);
+    create_ms[0] = now_ms() - t_begin - t_tables;  // host time spent pushing the bases (the tables build underneath)
     // coefficient records {u32 m, u32 c, u32 s, Fr coef} packed(1) (src/groth16.cpp:38, src/groth16.hpp:42-50) -> CSR by (m, c)
     csr_thread.join();
     if (!csr_err.empty()) throw std::range_error(csr_err);
@@ -449,15 +483,32 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
     n_long_ = (uint32_t)csr.longs.size();
     n_long_segs_ = (uint32_t)csr.segs.size();
     if (n_long_) {
-        long_rows_ = upload(ctx, csr.longs.data(), csr.longs.size() * sizeof(LongRow));
-        long_segs_ = upload(ctx, csr.segs.data(), csr.segs.size() * sizeof(LongRow));
+        long_rows_ = upload_up(csr.longs.data(), csr.longs.size() * sizeof(LongRow));
+        long_segs_ = upload_up(csr.segs.data(), csr.segs.size() * sizeof(LongRow));
         long_partial_ = dev_alloc((size_t)n_long_segs_ * 32);
     }
-    row_ptr_ = (uint32_t*)upload(ctx, csr.rp.data(), csr.rp.size() * 4);
-    coef_sig_ = (uint32_t*)upload(ctx, csr.sig.data(), csr.sig.size() * 4);
-    coef_val_ = upload(ctx, csr.val.data(), csr.val.size());
-    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+    row_ptr_ = (uint32_t*)upload_up(csr.rp.data(), csr.rp.size() * 4);
+    coef_sig_ = (uint32_t*)upload_up(csr.sig.data(), csr.sig.size() * 4);
+    coef_val_ = upload_up(csr.val.data(), csr.val.size());
+    UG_CUDA_CHECK(cudaStreamSynchronize(up));  // the host vectors of the CSR go out of scope below
 
+    // read the zero-point counts back and keep the maps that pay for a sort of their own
+    {
+        uint32_t h_counts[3] = {0, 0, 0};
+        UG_CUDA_CHECK(cudaMemcpyAsync(h_counts, d_counts, 12, cudaMemcpyDeviceToHost, ctx.stream));
+        UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+        const char* e = getenv("UGB_MSM_SKIP_INF");
+        const bool enabled = !(e && atoi(e) == 0) && wn > 0;
+        auto keep = [&](uint32_t*& skip, uint32_t* bm, uint64_t& out_count, uint32_t count, double thr) {
+            out_count = count;
+            if (bm && enabled && (double)count >= thr * (double)wn) skip = bm;
+            else if (bm) garbage.push_back(bm);
+        };
+        keep(skip_a_, bm_a, inf_points[0], h_counts[0], 0.15);
+        keep(skip_b_, bm_b, inf_points[1], h_counts[1], 0.04);
+        keep(skip_c_, bm_c, inf_points[2], h_counts[2], 0.15);
+    }
+    create_ms[2] = now_ms() - t_begin - create_ms[0];  // the rest of the wait until every table is built
     w_ = dev_alloc((size_t)w_chunk() * shard_world_ * 32);  // padded so that equal-sized slices can be all-gathered in place
     // padded like w_: slices of the transformed vectors travel between shards in equal chunks
     a_ = dev_alloc((size_t)h_chunk() * shard_world_ * 32);
