@@ -389,6 +389,31 @@ UG_HD void mont_sos_row(uint32_t* prev0, uint32_t* prev1, uint32_t tnext) {
     prev0[7] = addc(prev0[7], 0);
 }
 
+// T (16 limbs, < p * 2^256) -> T * 2^-256 mod p, fully reduced: eight fused "shift, bring in the next limb, reduce" rows.
+// The 9-limb window starts as T[0..7]; after every row it moves up one limb and the next limb of T enters at window position 7
+// (T[15] is added with the final fold).  64 + 8 multiplier operations.
+template <class P>
+UG_HD Fp<P> mont_reduce_512(const uint32_t* T) {
+    uint32_t e[8], o[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { e[k] = T[k]; o[k] = 0; }
+    mont_reduce_row<P>(e, o);
+    mont_sos_row<P>(e, o, T[8]);   // o column 0, e column 1
+    mont_sos_row<P>(o, e, T[9]);   // e column 0, o column 1
+    mont_sos_row<P>(e, o, T[10]);
+    mont_sos_row<P>(o, e, T[11]);
+    mont_sos_row<P>(e, o, T[12]);
+    mont_sos_row<P>(o, e, T[13]);
+    mont_sos_row<P>(e, o, T[14]);  // o column 0 (o[0] == 0), e column 1
+    Fp<P> r;
+    r.v[0] = add_cc(e[0], o[1]);
+#pragma unroll
+    for (int k = 1; k < 7; k++) r.v[k] = addc_cc(e[k], o[k + 1]);
+    r.v[7] = addc(e[7], T[15]);
+    fp_final_sub(r);
+    return r;
+}
+
 template <class P>
 UG_HD Fp<P> fp_mul_ks(const Fp<P>& x, const Fp<P>& y) {
     uint32_t T[16];
@@ -421,26 +446,7 @@ UG_HD Fp<P> fp_mul_ks(const Fp<P>& x, const Fp<P>& y) {
         for (int k = 1; k < 9; k++) T[4 + k] = addc_cc(T[4 + k], zm[k]);
         T[13] = addc_cc(T[13], 0); T[14] = addc_cc(T[14], 0); T[15] = addc(T[15], 0);
     }
-    // separate Montgomery reduction: the 9-limb window starts as T[0..7]; after every row it moves up one limb and the next
-    // limb of T enters at window position 7 (T[15] is added with the final fold)
-    uint32_t e[8], o[8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) { e[k] = T[k]; o[k] = 0; }
-    mont_reduce_row<P>(e, o);
-    mont_sos_row<P>(e, o, T[8]);   // o column 0, e column 1
-    mont_sos_row<P>(o, e, T[9]);   // e column 0, o column 1
-    mont_sos_row<P>(e, o, T[10]);
-    mont_sos_row<P>(o, e, T[11]);
-    mont_sos_row<P>(e, o, T[12]);
-    mont_sos_row<P>(o, e, T[13]);
-    mont_sos_row<P>(e, o, T[14]);  // o column 0 (o[0] == 0), e column 1
-    Fp<P> r;
-    r.v[0] = add_cc(e[0], o[1]);
-#pragma unroll
-    for (int k = 1; k < 7; k++) r.v[k] = addc_cc(e[k], o[k + 1]);
-    r.v[7] = addc(e[7], T[15]);
-    fp_final_sub(r);
-    return r;
+    return mont_reduce_512<P>(T);
 }
 
 // ---- FP64-assisted Montgomery product (sm_100a: B200 has a full-rate FP64 pipe that every kernel here leaves idle) -----------

@@ -163,6 +163,27 @@ __global__ void __launch_bounds__(256) k_bench_modmul_dfma(Fq* out, uint32_t see
     if (s.v[0] == 0x12345678u && s.v[7] == 1) out[0] = s;
 }
 
+// kinds 8 / 9: dependent Fq2 product chains, three complete Fq products (Karatsuba) vs lazy reduction (fq2_mul_lazy, curve.cuh)
+template <int LAZY>
+__global__ void __launch_bounds__(256) k_bench_fq2mul(Fq2* out, uint32_t seed) {
+    Fq2 a[2];
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        a[i] = Fq2::one();
+        a[i].a.v[0] += seed + threadIdx.x + i;
+        a[i].b.v[1] += seed * 3 + i;
+    }
+    for (int it = 0; it < MB_ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+            if (LAZY) { Fq2 r; fq2_mul_lazy(a[i].a, a[i].b, a[i ^ 1].a, a[i ^ 1].b, r.a, r.b); a[i] = r; }
+            else a[i] = fmul(a[i], a[i ^ 1]);
+        }
+    }
+    Fq2 s = fadd(a[0], a[1]);
+    if (s.a.v[0] == 0x12345678u && s.b.v[7] == 1) out[0] = s;
+}
+
 double bench_int_pipe(DeviceCtx& ctx, int kind) {
     ctx.activate();
     void* d = ctx.workspace("intbench", 256);
@@ -180,6 +201,8 @@ double bench_int_pipe(DeviceCtx& ctx, int kind) {
         else if (kind == 4) { k_bench_imad_wide_cout<<<blocks, 256, 0, ctx.stream>>>((uint32_t*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
         else if (kind == 6) { k_bench_dfma<<<blocks, 256, 0, ctx.stream>>>((double*)d, 7 + rep); ops = (double)blocks * 256 * 8 * IB_ITERS; }
         else if (kind == 7) { k_bench_modmul_dfma<<<blocks, 256, 0, ctx.stream>>>((Fq*)d, 7 + rep); ops = (double)blocks * 256 * 4 * MB_ITERS; }
+        else if (kind == 8) { k_bench_fq2mul<0><<<blocks, 256, 0, ctx.stream>>>((Fq2*)d, 7 + rep); ops = (double)blocks * 256 * 2 * MB_ITERS; }
+        else if (kind == 9) { k_bench_fq2mul<1><<<blocks, 256, 0, ctx.stream>>>((Fq2*)d, 7 + rep); ops = (double)blocks * 256 * 2 * MB_ITERS; }
         else if (kind == 5) { k_bench_modmul_ks<<<blocks, 256, 0, ctx.stream>>>((Fq*)d, 7 + rep); ops = (double)blocks * 256 * 4 * MB_ITERS; }
         else { k_bench_modmul<<<blocks, 256, 0, ctx.stream>>>((Fq*)d, 7 + rep); ops = (double)blocks * 256 * 4 * MB_ITERS; }
         UG_LAUNCH_CHECK(ctx);
