@@ -70,6 +70,31 @@ UG_HD Fq2 finv(const Fq2& x) {
     return r;
 }
 
+// ---- a*b - c*d with ONE Montgomery reduction (Fq) ---------------------------------------------------------------------------------
+// Both products as 512-bit integers, their difference (+ p * 2^256 when negative) reduced once: 2*64 + 72 = 200 multiplier
+// operations instead of 2*136.  Same canonical value as fsub(fmul(a, b), fmul(c, d)).
+// MEASURED AND OFF BY DEFAULT (UG_LAZY_MULSUB turns it on): in the G1 mixed addition (Y3 = R*(Q - X3) - Y1*PPP) it costs the
+// 128-register kernel a spill and the separate-reduction form its extra additions: msm_a 9.70 vs 9.55 ms, proof 74.2 vs 73.5 ms
+// (tools/r02_ab.sh).  The same idea pays in Fq2, where it removes a whole reduction per product (fq2_mul_lazy below).
+UG_HD Fq fmul_sub(const Fq& a, const Fq& b, const Fq& c, const Fq& d) {
+#if !defined(UG_LAZY_MULSUB)
+    return fp_sub(fp_mul(a, b), fp_mul(c, d));
+#else
+    uint32_t T0[16], T1[16];
+    mul8x8(a.v, b.v, T0);
+    mul8x8(c.v, d.v, T1);
+    T0[0] = sub_cc(T0[0], T1[0]);
+#pragma unroll
+    for (int k = 1; k < 16; k++) T0[k] = subc_cc(T0[k], T1[k]);
+    const uint32_t borrow = subc(0, 0);
+    T0[8] = add_cc(T0[8], FqParams::mod(0) & borrow);
+#pragma unroll
+    for (int k = 1; k < 7; k++) T0[8 + k] = addc_cc(T0[8 + k], FqParams::mod(k) & borrow);
+    T0[15] = addc(T0[15], FqParams::mod(7) & borrow);
+    return mont_reduce_512<FqParams>(T0);
+#endif
+}
+
 // ---- Fq2 product with LAZY reduction ------------------------------------------------------------------------------------
 // (a + b u)(c + d u) = (ac - bd) + ((a+b)(c+d) - ac - bd) u.  The three Karatsuba products are formed as full 512-bit integers
 // (mul8x8, 64 multiplier operations each) and only the two RESULT coordinates are Montgomery-reduced (mont_reduce_512, 72 each):
@@ -160,6 +185,11 @@ __device__ __forceinline__ Fq2c fmul(const Fq2c& x, const Fq2c& y) { return fq2c
 __device__ __forceinline__ Fq2c fsqr(const Fq2c& x) { return fq2c_sqr_call(x); }
 #endif
 
+UG_HD Fq2 fmul_sub(const Fq2& a, const Fq2& b, const Fq2& c, const Fq2& d) { return fsub(fmul(a, b), fmul(c, d)); }
+#if defined(__CUDACC__)
+__device__ __forceinline__ Fq2c fmul_sub(const Fq2c& a, const Fq2c& b, const Fq2c& c, const Fq2c& d) { return fsub(fmul(a, b), fmul(c, d)); }
+#endif
+
 // ---- points ---------------------------------------------------------------------------------
 template <class F>
 struct alignas(16) Affine {
@@ -246,7 +276,7 @@ UG_HD void pt_madd(XYZZ<F>& acc, const Affine<F>& q, bool neg) {
     F PPP = fmul(Pp, PP);
     F Qv = fmul(acc.X, PP);
     F X3 = fsub(fsub(fsqr(Rr), PPP), fdbl(Qv));
-    acc.Y = fsub(fmul(Rr, fsub(Qv, X3)), fmul(acc.Y, PPP));
+    acc.Y = fmul_sub(Rr, fsub(Qv, X3), acc.Y, PPP);
     acc.X = X3;
     acc.ZZ = fmul(acc.ZZ, PP);
     acc.ZZZ = fmul(acc.ZZZ, PPP);
@@ -272,7 +302,7 @@ UG_HD void pt_add(XYZZ<F>& acc, const XYZZ<F>& q) {
     F PPP = fmul(Pp, PP);
     F Qv = fmul(U1, PP);
     F X3 = fsub(fsub(fsqr(Rr), PPP), fdbl(Qv));
-    acc.Y = fsub(fmul(Rr, fsub(Qv, X3)), fmul(S1, PPP));
+    acc.Y = fmul_sub(Rr, fsub(Qv, X3), S1, PPP);
     acc.X = X3;
     acc.ZZ = fmul(fmul(acc.ZZ, q.ZZ), PP);
     acc.ZZZ = fmul(fmul(acc.ZZZ, q.ZZZ), PPP);

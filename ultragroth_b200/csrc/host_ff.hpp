@@ -117,6 +117,9 @@ inline HFp<P> fmul(const HFp<P>& x, const HFp<P>& y) {
 }
 template <class P>
 inline HFp<P> fsqr(const HFp<P>& x) { return fmul(x, x); }
+// a*b - c*d (the device code reduces the difference of the two products once; the host has no reason to)
+template <class P>
+inline HFp<P> fmul_sub(const HFp<P>& a, const HFp<P>& b, const HFp<P>& c, const HFp<P>& d) { return fsub(fmul(a, b), fmul(c, d)); }
 template <class P>
 inline HFp<P> to_mont(const HFp<P>& a) { return fmul(a, HFp<P>::rsquared()); }
 template <class P>
@@ -154,6 +157,7 @@ inline HFq2 fmul(const HFq2& x, const HFq2& y) {
     HFq s = fmul(fadd(x.a, x.b), fadd(y.a, y.b));
     HFq2 r; r.a = fsub(ac, bd); r.b = fsub(fsub(s, ac), bd); return r;
 }
+inline HFq2 fmul_sub(const HFq2& a, const HFq2& b, const HFq2& c, const HFq2& d) { return fsub(fmul(a, b), fmul(c, d)); }
 inline HFq2 fsqr(const HFq2& x) {
     HFq ab = fmul(x.a, x.b);
     HFq2 r; r.a = fmul(fadd(x.a, x.b), fsub(x.a, x.b)); r.b = fadd(ab, ab); return r;

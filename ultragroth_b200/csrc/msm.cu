@@ -75,6 +75,20 @@ void msm_inf_bitmap_async(DeviceCtx& ctx, int group, const void* d_bases, uint64
     else UG_KERNEL(ctx, "k_inf_bitmap", k_inf_bitmap<Fq2c><<<blocks, 256, 0, ctx.stream>>>((const Affine<Fq2c>*)d_bases, (uint32_t)n, d_bitmap, combine ? 1 : 0, d_count));
 }
 
+uint64_t msm_bitmap_and(DeviceCtx& ctx, const uint32_t* d_x, const uint32_t* d_y, uint64_t n_points, uint32_t* d_out) {
+    ctx.activate();
+    const uint32_t words = (uint32_t)((n_points + 31) / 32);
+    if (words == 0) return 0;
+    uint32_t* d_count = (uint32_t*)ctx.workspace("msm.inf_count", 16);
+    UG_CUDA_CHECK(cudaMemsetAsync(d_count, 0, 4, ctx.stream));
+    const int blocks = (int)std::min<uint32_t>((words + 255) / 256, (uint32_t)ctx.sm_count * 4);
+    UG_KERNEL(ctx, "k_bitmap_and", k_bitmap_and<<<blocks, 256, 0, ctx.stream>>>(d_x, d_y, words, d_out, d_count));
+    uint32_t h = 0;
+    UG_CUDA_CHECK(cudaMemcpyAsync(&h, d_count, 4, cudaMemcpyDeviceToHost, ctx.stream));
+    UG_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+    return h;
+}
+
 uint64_t msm_inf_bitmap(DeviceCtx& ctx, int group, const void* d_bases, uint64_t n, uint32_t* d_bitmap, bool combine) {
     ctx.activate();
     if (n == 0) return 0;

@@ -140,6 +140,18 @@ __global__ void __launch_bounds__(256) k_inf_bitmap(const Affine<F>* __restrict_
     if (lane == 0 && local) atomicAdd(count, local);
 }
 
+// out = x & y over `words` bitmap words; *count += set bits of the result
+__global__ void __launch_bounds__(256) k_bitmap_and(const uint32_t* __restrict__ x, const uint32_t* __restrict__ y, uint32_t words,
+                                                    uint32_t* __restrict__ out, uint32_t* __restrict__ count) {
+    uint32_t local = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < words; i += gridDim.x * blockDim.x) {
+        const uint32_t v = x[i] & y[i];
+        out[i] = v;
+        local += __popc(v);
+    }
+    if (local) atomicAdd(count, local);
+}
+
 // ---- exclusive scan of the histogram (3 small launches; tile = 2048 counters) -----------------
 constexpr int SCAN_BS = 256;
 constexpr int SCAN_TILE = 2048;

@@ -66,6 +66,8 @@ void msm_sort_digits(DeviceCtx& ctx, const uint8_t* d_scalars, const uint32_t* d
 // bitmap of the points at infinity among n affine bases (group 1: G1, 2: G2); combine = AND into the existing bitmap (points that
 // are infinite in ALL the arrays combined).  Returns the number of set bits.  d_bitmap: (n + 31) / 32 words, device.
 uint64_t msm_inf_bitmap(DeviceCtx& ctx, int group, const void* d_bases, uint64_t n, uint32_t* d_bitmap, bool combine);
+// d_out = d_x & d_y (bitmaps over n_points points); returns the number of set bits
+uint64_t msm_bitmap_and(DeviceCtx& ctx, const uint32_t* d_x, const uint32_t* d_y, uint64_t n_points, uint32_t* d_out);
 // the same, enqueued only: the number of set bits is ADDED to *d_count (device) -- zero it first; nothing is synchronised
 void msm_inf_bitmap_async(DeviceCtx& ctx, int group, const void* d_bases, uint64_t n, uint32_t* d_bitmap, bool combine, uint32_t* d_count);
 

@@ -507,6 +507,25 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
         keep(skip_a_, bm_a, inf_points[0], h_counts[0], 0.15);
         keep(skip_b_, bm_b, inf_points[1], h_counts[1], 0.04);
         keep(skip_c_, bm_c, inf_points[2], h_counts[2], 0.15);
+        // two classes whose zero points nearly coincide (>= 90 % of the larger map survives the AND) share ONE sort on the common map:
+        // the few points only one of them could have skipped cost less than a digit sort (in the UltraGroth benchmark circuit A has
+        // no terms for the chunk signals and the final-round C has none for chunks + frequencies: the same set but for 2^16 signals)
+        auto merge = [&](uint32_t*& x, uint32_t*& y, uint64_t cx, uint64_t cy) -> bool {
+            if (!x || !y || x == y) return false;
+            uint32_t* both = (uint32_t*)dev_alloc(bm_words);
+            const uint64_t c = msm_bitmap_and(ctx, x, y, wn, both);
+            if ((double)c >= 0.9 * (double)std::max(cx, cy)) {
+                garbage.push_back(x);
+                if (y != x) garbage.push_back(y);
+                x = y = both;
+                return true;
+            }
+            garbage.push_back(both);
+            return false;
+        };
+        // at most one pair is merged (a third class joining would need its map re-pointed as well)
+        if (!merge(skip_a_, skip_c_, inf_points[0], inf_points[2]))
+            if (!merge(skip_a_, skip_b_, inf_points[0], inf_points[1])) merge(skip_b_, skip_c_, inf_points[1], inf_points[2]);
     }
     create_ms[2] = now_ms() - t_begin - create_ms[0];  // the rest of the wait until every table is built
     w_ = dev_alloc((size_t)w_chunk() * shard_world_ * 32);  // padded so that equal-sized slices can be all-gathered in place
@@ -534,6 +553,8 @@ void ProverDevice::release() {
     void** ptrs[] = {&long_rows_, &long_segs_, &long_partial_, &A_, &B1_, &B2_, &C_, &H_, &C1_, (void**)&idx_c1_, (void**)&idx_c2_, (void**)&row_ptr_,
                      (void**)&skip_a_, (void**)&skip_b_, (void**)&skip_c_,
                      (void**)&coef_sig_, &coef_val_, &w_, &a_, &b_, &c_};
+    if (skip_b_ == skip_a_) skip_b_ = nullptr;  // merged classes share one map
+    if (skip_c_ == skip_a_ || skip_c_ == skip_b_) skip_c_ = nullptr;
     if (w_alt_) {  // w_ may be on either of the two batch buffers
         w_ = wbuf_[0];
         cudaFree(w_alt_);
@@ -584,9 +605,17 @@ void ProverDevice::phase_witness_msms() {
     const MsmConfig* wcfg = pre_ ? &cfg_w_ : nullptr;
     const bool c_in_w = c_shares_witness_sort_;
     if (!skip_a_ || !skip_b_ || (c_in_w && !skip_c_)) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "w", ph.dw, wcfg);
+    // one sort per DISTINCT map (classes merged at create share a pointer)
     if (skip_a_) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wa", ph.dwa, wcfg, skip_a_);
-    if (skip_b_) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wb", ph.dwb, wcfg, skip_b_);
-    if (c_in_w && skip_c_) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wc", ph.dwc, wcfg, skip_c_);
+    if (skip_b_) {
+        if (skip_b_ == skip_a_) ph.dwb = ph.dwa;
+        else msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wb", ph.dwb, wcfg, skip_b_);
+    }
+    if (c_in_w && skip_c_) {
+        if (skip_c_ == skip_a_) ph.dwc = ph.dwa;
+        else if (skip_c_ == skip_b_) ph.dwc = ph.dwb;
+        else msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wc", ph.dwc, wcfg, skip_c_);
+    }
     ph.dA = skip_a_ ? &ph.dwa : &ph.dw;
     ph.dB = skip_b_ ? &ph.dwb : &ph.dw;
     ph.dC = c_in_w ? (skip_c_ ? &ph.dwc : &ph.dw) : &ph.dc;
