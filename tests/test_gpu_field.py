@@ -50,7 +50,7 @@ def test_mul_unreduced_first_operand(ctx, field, mod):
 
 @pytest.mark.parametrize("field,mod", [(0, bn.R), (1, bn.Q)])
 def test_fp64_assisted_product_bit_exact(ctx, field, mod):
-    """fp_mul_dfma (csrc/ff.cuh): x*y on the integer multiplier, the m*p half of the Montgomery reduction on the FP64 pipe (exact
+    """fp_mul_dfma (csrc/ff_variants.cuh): x*y on the integer multiplier, the m*p half of the Montgomery reduction on the FP64 pipe (exact
     52-bit limb products from round-towards-zero FMAs).  Same values as Fr_rawMMul for every input, including the rare case where
     the dropped low columns borrow through bit 256 (inputs built so that x*y mod 2^256 = 2^256 - L with L small)."""
     rng = random.Random(4321 + field)

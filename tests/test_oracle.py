@@ -309,12 +309,12 @@ def test_oracle_reproduces_golden_testdata_proof():
 
 
 def test_karatsuba_product_matches_cios_product_on_cpu(tmp_path):
-    """fp_mul_ks (Karatsuba + separate Montgomery reduction, ff.cuh) against fp_mul -- itself pinned to the reference's field code
+    """fp_mul_ks (Karatsuba + separate Montgomery reduction, ff_variants.cuh) against fp_mul -- itself pinned to the reference's field code
     above -- on 2*10^5 random and edge-case operand pairs per field, through the host build of the device limb code."""
     import subprocess
     src = tmp_path / "ks.cpp"
     src.write_text(r'''
-#include "ff.cuh"
+#include "ff_variants.cuh"
 #include <cstdio>
 #include <cstdlib>
 using namespace ug;
@@ -335,6 +335,114 @@ template <class F> int run() {
 int main() { int b = run<Fq>() + run<Fr>(); printf("mismatches %d\n", b); return b != 0; }
 ''')
     exe = tmp_path / "ks"
+    root = os.path.dirname(HERE)
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-I", os.path.join(root, "ultragroth_b200", "csrc"), str(src), "-o", str(exe)])
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0 and "mismatches 0" in out.stdout, out.stdout + out.stderr
+
+
+def test_fp64_assisted_product_matches_cios_product_on_cpu(tmp_path):
+    """fp_mul_dfma (ff_variants.cuh: the m*p half of the reduction from exact 52-bit limb products made by round-towards-zero FMAs)
+    against fp_mul on the host build of the device limb code (the FMAs run on the host FPU in FE_TOWARDZERO mode): random pairs,
+    edge values, and inputs CONSTRUCTED so that x*y mod 2^256 = 2^256 - L with L of every magnitude up to 2^222 -- the case where the
+    dropped low columns borrow through bit 256 and the one-unit repair must fire."""
+    import subprocess
+    src = tmp_path / "dfma.cpp"
+    src.write_text(r'''
+#include "ff_variants.cuh"
+#include <cstdio>
+#include <random>
+using namespace ug;
+static void mulmod256(const uint32_t* a, const uint32_t* b, uint32_t* r) {
+    uint32_t out[8];
+    unsigned __int128 acc = 0;
+    for (int k = 0; k < 8; k++) {
+        for (int i = 0; i <= k; i++) acc += (unsigned __int128)a[i] * b[k - i];
+        out[k] = (uint32_t)acc;
+        acc >>= 32;
+    }
+    for (int k = 0; k < 8; k++) r[k] = out[k];
+}
+template <class F> long run(int iters, uint64_t seed) {
+    std::mt19937_64 g(seed);
+    long bad = 0;
+    for (int it = 0; it < iters; it++) {
+        F x, y;
+        for (int i = 0; i < 8; i += 2) { uint64_t r = g(); x.v[i] = (uint32_t)r; x.v[i + 1] = (uint32_t)(r >> 32); r = g(); y.v[i] = (uint32_t)r; y.v[i + 1] = (uint32_t)(r >> 32); }
+        x.v[7] &= 0x3fffffffu; y.v[7] &= 0x3fffffffu; fp_final_sub(x); fp_final_sub(y);
+        const int m = it % 9;
+        if (m == 0) x = F::zero();
+        if (m == 1) { x = F::modulus(); x.v[0] -= 1; y = x; }
+        if (m == 2) y = F::one();
+        if (m >= 5) {  // x = (2^256 - L) * y^-1 mod 2^256
+            y.v[0] |= 1u;
+            uint32_t inv[8] = {1, 0, 0, 0, 0, 0, 0, 0};
+            for (int rnd = 0; rnd < 9; rnd++) {
+                uint32_t t[8], tm[8];
+                mulmod256(y.v, inv, t);
+                uint64_t borrow = 0;
+                for (int k = 0; k < 8; k++) { uint64_t d = (uint64_t)(k == 0 ? 2 : 0) - t[k] - borrow; tm[k] = (uint32_t)d; borrow = (d >> 63) & 1; }
+                mulmod256(inv, tm, inv);
+            }
+            uint32_t L[8], tgt[8];
+            const int bits = 1 + (int)(g() % 222);
+            for (int k = 0; k < 8; k++) { L[k] = (uint32_t)g(); const int lo = 32 * k; if (lo >= bits) L[k] = 0; else if (lo + 32 > bits) L[k] &= (1u << (bits - lo)) - 1u; }
+            if (m == 8) { for (int k = 0; k < 8; k++) L[k] = 0; L[0] = 1; }
+            uint64_t borrow = 0;
+            for (int k = 0; k < 8; k++) { uint64_t d = (uint64_t)0 - L[k] - borrow; tgt[k] = (uint32_t)d; borrow = (d >> 63) & 1; }
+            mulmod256(tgt, inv, x.v);
+        }
+        if (!(fp_mul(x, y) == fp_mul_dfma(x, y))) bad++;
+    }
+    return bad;
+}
+int main() { long b = run<Fq>(60000, 1) + run<Fr>(60000, 2); printf("mismatches %ld\n", b); return b != 0; }
+''')
+    exe = tmp_path / "dfma"
+    root = os.path.dirname(HERE)
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-frounding-math", "-I", os.path.join(root, "ultragroth_b200", "csrc"), str(src), "-o", str(exe)])
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0 and "mismatches 0" in out.stdout, out.stdout + out.stderr
+
+
+def test_lazy_fq2_product_matches_three_full_products_on_cpu(tmp_path):
+    """fq2_mul_lazy (curve.cuh: three 512-bit Karatsuba products, two Montgomery reductions -- the product the G2 kernels use) against
+    the plain Fq2 product of three complete Fq products, on the host build of the device limb code."""
+    import subprocess
+    src = tmp_path / "fq2.cpp"
+    src.write_text(r'''
+#include "curve.cuh"
+#include <cstdio>
+#include <random>
+using namespace ug;
+int main() {
+    std::mt19937_64 g(5);
+    auto rnd = [&](Fq& v) { for (int i = 0; i < 8; i += 2) { uint64_t r = g(); v.v[i] = (uint32_t)r; v.v[i + 1] = (uint32_t)(r >> 32); } v.v[7] &= 0x3fffffffu; fp_final_sub(v); };
+    long bad = 0;
+    Fq pm1 = Fq::modulus(); pm1.v[0] -= 1;
+    for (int it = 0; it < 200000; it++) {
+        Fq2 x, y;
+        rnd(x.a); rnd(x.b); rnd(y.a); rnd(y.b);
+        const int m = it % 11;
+        if (m == 0) { x.a = pm1; x.b = pm1; y.a = pm1; y.b = pm1; }
+        if (m == 1) x.a = Fq::zero();
+        if (m == 2) { x.b = pm1; y.b = pm1; x.a = Fq::zero(); y.a = Fq::zero(); }
+        if (m == 3) x = Fq2::zero();
+        if (m == 4) y = Fq2::one();
+        Fq ac = fp_mul(x.a, y.a), bd = fp_mul(x.b, y.b), s = fp_mul(fp_add(x.a, x.b), fp_add(y.a, y.b));
+        Fq2 want, got;
+        want.a = fp_sub(ac, bd);
+        want.b = fp_sub(fp_sub(s, ac), bd);
+        fq2_mul_lazy(x.a, x.b, y.a, y.b, got.a, got.b);
+        if (!(want == got)) bad++;
+        Fq w2 = fp_sub(fp_mul(x.a, y.a), fp_mul(x.b, y.b));
+        if (!(w2 == want.a)) bad++;
+    }
+    printf("mismatches %ld\n", bad);
+    return bad != 0;
+}
+''')
+    exe = tmp_path / "fq2"
     root = os.path.dirname(HERE)
     subprocess.check_call(["g++", "-O2", "-std=c++17", "-I", os.path.join(root, "ultragroth_b200", "csrc"), str(src), "-o", str(exe)])
     out = subprocess.run([str(exe)], capture_output=True, text=True)

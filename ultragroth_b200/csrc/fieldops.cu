@@ -1,6 +1,7 @@
 // Element-wise Fr / Fq vector kernels (the parity kernels for build/fr.asm / fq.asm, and the
 // pointwise loops of src/groth16.cpp:100-108).  HBM-bound: 96 B of traffic per element.
 #include "fieldops.hpp"
+#include "ff_variants.cuh"
 #include "memops.cuh"
 #include <algorithm>
 

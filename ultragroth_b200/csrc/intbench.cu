@@ -2,6 +2,7 @@
 // "imad_peak must be microbenchmarked on the box").  Every thread runs 8 independent chains so the
 // 4-cycle IMAD latency is covered without relying on occupancy.
 #include "curve.cuh"
+#include "ff_variants.cuh"
 #include "device.hpp"
 
 namespace ug {
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(256) k_bench_modmul(Fq* out, uint32_t seed) {
     if (s.v[0] == 0x12345678u && s.v[7] == 1) out[0] = s;
 }
 
-// kind 5: the same chains on the Karatsuba + separate-reduction product (fp_mul_ks, ff.cuh)
+// kind 5: the same chains on the Karatsuba + separate-reduction product (fp_mul_ks, ff_variants.cuh)
 __global__ void __launch_bounds__(256) k_bench_modmul_ks(Fq* out, uint32_t seed) {
     Fq a[4];
 #pragma unroll
@@ -147,7 +148,7 @@ __global__ void __launch_bounds__(256) k_bench_dfma(double* out, uint32_t seed) 
     if (s == 0.12345) out[0] = s;
 }
 
-// kind 7: kind 2's dependent chains on the FP64-assisted product (fp_mul_dfma, ff.cuh)
+// kind 7: kind 2's dependent chains on the FP64-assisted product (fp_mul_dfma, ff_variants.cuh)
 __global__ void __launch_bounds__(256) k_bench_modmul_dfma(Fq* out, uint32_t seed) {
     Fq a[4];
 #pragma unroll

@@ -1,5 +1,6 @@
 // MSM driver: launches the kernels of msm.cuh; the host combines the per-level / per-window partial sums (msm_host.cpp).
 #include "msm.cuh"
+#include "msm_variants.cuh"
 #include "msm.hpp"
 
 #include <algorithm>
