@@ -414,12 +414,24 @@ def sharded_leg(args, torch, dist, world, rank, local, zkey, wt_np, vkj, ultra, 
     tt = torch.tensor([t, t_h], dtype=torch.float64, device="cuda")
     dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     t, t_h = float(tt[0]), float(tt[1])
+    # where the latency goes: two TRACED proofs after the timed ones (the stream is drained at every seam, so the phases are
+    # serialised and sum to more than ms_per_proof); the max over ranks per phase shows which phase the slowest shard holds up
+    trace = {}
+    for _ in range(2):
+        sp.prove2(wt_np, rk=rk if ultra else None, comm=comm, trace=trace)
+    names = ["upload_slice", "all_gather_witness", "round_msm_and_exchange", "lookup", "h_transform", "witness_msms", "scatter_wait",
+             "h_msm_and_finish", "exchange_partials", "assemble"]
+    tl = torch.tensor([trace.get(k, 0.0) / 2 for k in names], dtype=torch.float64, device="cuda")
+    tl_max = tl.clone()
+    dist.all_reduce(tl_max, op=dist.ReduceOp.MAX)
     n = 1 << args.logn
     rec = {"scaling": "strong", "ms_per_proof": 1000.0 * t / args.steps, "proofs_per_s": args.steps / t, "verified": ok,
            "parallelism": f"bases, witness upload, H pipeline and MSMs sharded x{world}; one proof at a time",
            "g1_msm_h": {"points": n, "ms": 1000.0 * t_h, "points_per_s": n / t_h,
                         "what": "H MSM of the proof sharded by point range: k_h_final + digit sort + bucket accumulation + reduction per rank, max over ranks"},
-           "create_s": round(t_create, 2)}
+           "create_s": round(t_create, 2),
+           "timeline_rank0_ms": {k: round(float(v), 3) for k, v in zip(names, tl.tolist()) if v > 0},
+           "timeline_max_over_ranks_ms": {k: round(float(v), 3) for k, v in zip(names, tl_max.tolist()) if v > 0}}
     sp.close()
     return rec
 

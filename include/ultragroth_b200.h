@@ -168,7 +168,10 @@ int ugb_prover_prove_batch(void* prover_object, uint32_t count, const void* cons
 typedef struct ugb_shard_layout {
     void *w, *a, *b, *c;             /* device buffers: witness (world * w_chunk signals), a / b / c (world * h_chunk elements), 32 B each */
     uint64_t nVars, domainSize;
-    uint64_t w_chunk, h_chunk;       /* rank r owns signals [r * w_chunk, min(nVars, (r+1) * w_chunk)) and H points likewise */
+    uint64_t w_chunk, h_chunk;       /* rank r UPLOADS signals [r * w_chunk, min(nVars, (r+1) * w_chunk)) and owns H points likewise; the
+                                      * witness-paired bases (A, B1, B2, C) it owns are those of signals r, r + world, r + 2 world, ...
+                                      * (interleaved: balanced bucket work whatever the circuit's signal order), so
+                                      * ugb_shard_witness_msms needs the whole witness resident (after the all-gather) */
     uint32_t rank, world;
     int device;
     void* stream;                    /* cudaStream_t every phase is enqueued on */

@@ -226,6 +226,23 @@ __global__ void __launch_bounds__(SCAN_BS) k_scan_apply(const uint32_t* __restri
 // [t*L, (t+1)*L), L = ceil(M/T).  Outputs: buckets[key] for runs strictly inside the slice,
 // (pkeys, ppts)[2t], [2t+1] for the first and last run of the slice.  key_off / key_none: several MSMs that share one digit sort
 // are reduced together (msm.cu: batch): pkeys carry key + key_off (position in the concatenated bucket array), key_none = "no run".
+// The next non-empty bucket after `key`: the smallest k > key with starts[k + 1] > pos.  Dense digit distributions find it at the
+// first or second probe; a shard that holds only small scalars leaves ~2^21 empty buckets between two windows, and a linear walk
+// over them stalls one thread (and with it its whole launch: 5 ms kernels at 2 % pipe use on shard 0 of 8) -- so after two probes
+// the search is binary.  Caller guarantees pos < starts[NB].
+__device__ __forceinline__ void next_bucket(const uint32_t* __restrict__ starts, uint32_t NB, uint32_t& key, uint32_t pos, uint32_t& end) {
+    key++; end = starts[key + 1];
+    if (end > pos) return;
+    key++; end = starts[key + 1];
+    if (end > pos) return;
+    uint32_t a = key + 1, b = NB - 1;
+    while (a < b) {
+        uint32_t mid = (a + b) >> 1;
+        if (starts[mid + 1] > pos) b = mid; else a = mid + 1;
+    }
+    key = a; end = starts[key + 1];
+}
+
 template <class F>
 __global__ void __launch_bounds__(128, sizeof(F) == 32 ? 4 : 1) k_accumulate(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
                                                     const uint32_t* __restrict__ starts, uint32_t NB,
@@ -261,7 +278,7 @@ __global__ void __launch_bounds__(128, sizeof(F) == 32 ? 4 : 1) k_accumulate(con
             if (first) { pkeys[2 * t] = key + key_off; st_g(&ppts[2 * t], acc); first = false; }
             else st_g(&buckets[key], acc);
             acc = XYZZ<F>::inf();
-            do { key++; end = starts[key + 1]; } while (end <= pos);
+            next_bucket(starts, NB, key, pos, end);
         }
         // prefetch the next point while this one is being added
         uint32_t e_next = 0;
@@ -317,7 +334,7 @@ __global__ void __launch_bounds__(128, MINB) k_accumulate_s(const Affine<F>* __r
             if (first) { pkeys[2 * t] = key + key_off; st_g(&ppts[2 * t], acc.get()); first = false; }
             else st_g(&buckets[key], acc.get());
             acc.set_inf();
-            do { key++; end = starts[key + 1]; } while (end <= pos);
+            next_bucket(starts, NB, key, pos, end);
         }
         const bool neg = (e >> 31) != 0;
         const Affine<F> cur = pt;

@@ -203,13 +203,19 @@ ZkeyData zkey_data_from_file(const BinFile& zkey, const ZkeyHeader& h) {
     return z;
 }
 
-// out[idx[i] - lo] = in[i] for idx[i] in [lo, hi): places the final-round C points at their witness slots
-__global__ void __launch_bounds__(256) k_scatter_affine(const G1Affine* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t count, uint32_t lo,
-                                                        uint32_t hi, G1Affine* __restrict__ out) {
+// out[idx[i] / world] = in[i] for the signals idx[i] this shard owns (idx[i] % world == rank): places the final-round C points at
+// their witness slots (world = 1: every slot)
+__global__ void __launch_bounds__(256) k_scatter_affine(const G1Affine* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t count, uint32_t world,
+                                                        uint32_t rank, G1Affine* __restrict__ out) {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
         const uint32_t s = idx[i];
-        if (s >= lo && s < hi) st_g(&out[s - lo], ld_nc(&in[i]));
+        if (s % world == rank) st_g(&out[s / world], ld_nc(&in[i]));
     }
+}
+
+// out[j] = first + j * stride: the signal of the j-th resident witness-paired point of a shard
+__global__ void __launch_bounds__(256) k_iota_strided(uint32_t* __restrict__ out, uint32_t count, uint32_t first, uint32_t stride) {
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < count; j += gridDim.x * blockDim.x) out[j] = first + j * stride;
 }
 
 namespace {
@@ -305,7 +311,8 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
     shard_world_ = shard_world;
     shard_range(nVars, shard_world, shard_rank, w_lo_, w_hi_);
     shard_range(domainSize, shard_world, shard_rank, h_lo_, h_hi_);
-    const uint64_t wn = w_hi_ - w_lo_, hn = h_hi_ - h_lo_;
+    own_cnt_ = nVars > shard_rank ? ((uint64_t)nVars - shard_rank + shard_world - 1) / shard_world : 0;
+    const uint64_t wn = own_cnt_, hn = h_hi_ - h_lo_;
     tabs_.reset(new NttTables(*ctx_));
     DeviceCtx& ctx = *ctx_;
     ctx.activate();
@@ -352,6 +359,22 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
         if (bytes) UG_CUDA_CHECK(cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, up));
         return p;
     };
+    // this shard's points of a witness-paired array: the whole array when unsharded, else points rank, rank + world, ... gathered on
+    // the host (threads over ranges of j) into a buffer that lives until the end of construct
+    std::vector<std::vector<uint8_t>> staged;
+    auto upload_own = [&](const uint8_t* src, size_t elem) -> void* {
+        if (shard_world == 1) return upload_up(src, (size_t)wn * elem);
+        staged.emplace_back((size_t)wn * elem);
+        uint8_t* dst = staged.back().data();
+        const unsigned nt = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(8, wn >> 16));
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < nt; t++)
+            th.emplace_back([=]() {
+                for (uint64_t j = wn * t / nt; j < wn * (t + 1) / nt; j++) memcpy(dst + j * elem, src + ((uint64_t)shard_rank + j * shard_world) * elem, elem);
+            });
+        for (auto& x : th) x.join();
+        return upload_up(dst, (size_t)wn * elem);
+    };
     auto landed = [&]() {  // the compute stream waits for everything pushed on the upload stream so far
         cudaEvent_t e;
         UG_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -389,15 +412,20 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
     MsmConfig tmp;
     if (pre_) ctx.workspace("msm.table_tmp", std::max<uint64_t>(wn, hn) * sizeof(Jac<Fq2c>) + 256);  // sized once: growing it later would drain the stream
 
-    A_ = upload_up(zk.A + w_lo_ * 64, (size_t)wn * 64);
+    if (shard_world > 1 && wn) {
+        own_idx_ = (uint32_t*)dev_alloc((size_t)wn * 4);
+        const int blocks = (int)std::min<uint64_t>((wn + 255) / 256, (uint64_t)ctx.sm_count * 8);
+        UG_KERNEL(ctx, "k_iota_strided", k_iota_strided<<<blocks, 256, 0, ctx.stream>>>(own_idx_, (uint32_t)wn, shard_rank, shard_world));
+    }
+    A_ = upload_own(zk.A, 64);
     landed();
     bitmap(bm_a, 0, 1, A_, false);
     tabulate(A_, 1, wn, cfg_w_);
-    B1_ = upload_up(zk.B1 + w_lo_ * 64, (size_t)wn * 64);
+    B1_ = upload_own(zk.B1, 64);
     landed();
     bitmap(bm_b, 1, 1, B1_, false);
     tabulate(B1_, 1, wn, tmp);
-    B2_ = upload_up(zk.B2 + w_lo_ * 128, (size_t)wn * 128);
+    B2_ = upload_own(zk.B2, 128);
     landed();
     bitmap(bm_b, 1, 2, B2_, true);
     tabulate(B2_, 2, wn, tmp);
@@ -406,13 +434,22 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
         need(zk.C_bytes, (uint64_t)nc * 64, "pointsC");
         // C pairs with witness[nPublic+1 ..] (src/groth16.cpp:64): pad with points at infinity so that the
         // C MSM reuses the sorted digits of the full witness
-        // slot i of the padded array = pointsC[i - (nPublic+1)] for i > nPublic, infinity below; keep [w_lo_, w_hi_)
+        // slot i of the padded array = pointsC[i - (nPublic+1)] for i > nPublic, infinity below; keep this shard's slots
         C_ = dev_alloc((size_t)wn * 64);
-        UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, std::max<size_t>((size_t)wn * 64, 16), up));
-        {
-            const uint64_t first = std::max<uint64_t>(w_lo_, (uint64_t)nPublic + 1);
-            if (first < w_hi_)
-                UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)C_ + (first - w_lo_) * 64, zk.C + (first - nPublic - 1) * 64, (size_t)(w_hi_ - first) * 64, cudaMemcpyHostToDevice, up));
+        if (shard_world == 1) {
+            UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, std::max<size_t>((size_t)wn * 64, 16), up));
+            const uint64_t first = (uint64_t)nPublic + 1;
+            if (first < nVars)
+                UG_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)C_ + first * 64, zk.C, (size_t)(nVars - first) * 64, cudaMemcpyHostToDevice, up));
+        } else if (wn) {
+            staged.emplace_back((size_t)wn * 64);
+            uint8_t* dst = staged.back().data();
+            for (uint64_t j = 0; j < wn; j++) {
+                const uint64_t sgn = (uint64_t)shard_rank + j * shard_world;
+                if (sgn > nPublic) memcpy(dst + j * 64, zk.C + (sgn - nPublic - 1) * 64, 64);
+                else memset(dst + j * 64, 0, 64);
+            }
+            UG_CUDA_CHECK(cudaMemcpyAsync(C_, dst, (size_t)wn * 64, cudaMemcpyHostToDevice, up));
         }
         c_shares_witness_sort_ = true;
         landed();
@@ -455,7 +492,7 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
             UG_CUDA_CHECK(cudaMemsetAsync(C_, 0, std::max<size_t>((size_t)wn * 64, 16), ctx.stream));
             if (n_c2_) {
                 const int blocks = (int)std::min<uint64_t>(((uint64_t)n_c2_ + 255) / 256, (uint64_t)ctx.sm_count * 8);
-                UG_KERNEL(ctx, "k_scatter_affine", k_scatter_affine<<<blocks, 256, 0, ctx.stream>>>((const G1Affine*)c2, idx_c2_, n_c2_, (uint32_t)w_lo_, (uint32_t)w_hi_, (G1Affine*)C_));
+                UG_KERNEL(ctx, "k_scatter_affine", k_scatter_affine<<<blocks, 256, 0, ctx.stream>>>((const G1Affine*)c2, idx_c2_, n_c2_, shard_world, shard_rank, (G1Affine*)C_));
             }
             c_shares_witness_sort_ = true;
             bitmap(bm_c, 2, 1, C_, false);
@@ -551,7 +588,7 @@ void ProverDevice::release() {
     cudaSetDevice(ctx_->device);
     cudaStreamSynchronize(ctx_->stream);
     void** ptrs[] = {&long_rows_, &long_segs_, &long_partial_, &A_, &B1_, &B2_, &C_, &H_, &C1_, (void**)&idx_c1_, (void**)&idx_c2_, (void**)&row_ptr_,
-                     (void**)&skip_a_, (void**)&skip_b_, (void**)&skip_c_,
+                     (void**)&skip_a_, (void**)&skip_b_, (void**)&skip_c_, (void**)&own_idx_,
                      (void**)&coef_sig_, &coef_val_, &w_, &a_, &b_, &c_};
     if (skip_b_ == skip_a_) skip_b_ = nullptr;  // merged classes share one map
     if (skip_c_ == skip_a_ || skip_c_ == skip_b_) skip_c_ = nullptr;
@@ -600,21 +637,23 @@ void ProverDevice::phase_witness_msms() {
     mark_stage(0);
     // the four witness MSMs read the same scalars (src/groth16.cpp:53-64): ONE digit sort serves every array that has no zero-point
     // map of its own; arrays with many points at infinity get a sort that skips them (skip_a_ / skip_b_ / skip_c_)
-    const uint8_t* wsl = (const uint8_t*)w_ + w_lo_ * 32;
-    const uint64_t wn = w_hi_ - w_lo_;
+    // resident point j pairs with signal own_idx_[j] (null = j: unsharded) of the whole witness
+    const uint8_t* wsl = (const uint8_t*)w_;
+    const uint32_t* widx = own_idx_;
+    const uint64_t wn = own_cnt_;
     const MsmConfig* wcfg = pre_ ? &cfg_w_ : nullptr;
     const bool c_in_w = c_shares_witness_sort_;
-    if (!skip_a_ || !skip_b_ || (c_in_w && !skip_c_)) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "w", ph.dw, wcfg);
+    if (!skip_a_ || !skip_b_ || (c_in_w && !skip_c_)) msm_sort_digits(ctx, wsl, widx, wn, 0, "w", ph.dw, wcfg);
     // one sort per DISTINCT map (classes merged at create share a pointer)
-    if (skip_a_) msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wa", ph.dwa, wcfg, skip_a_);
+    if (skip_a_) msm_sort_digits(ctx, wsl, widx, wn, 0, "wa", ph.dwa, wcfg, skip_a_);
     if (skip_b_) {
         if (skip_b_ == skip_a_) ph.dwb = ph.dwa;
-        else msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wb", ph.dwb, wcfg, skip_b_);
+        else msm_sort_digits(ctx, wsl, widx, wn, 0, "wb", ph.dwb, wcfg, skip_b_);
     }
     if (c_in_w && skip_c_) {
         if (skip_c_ == skip_a_) ph.dwc = ph.dwa;
         else if (skip_c_ == skip_b_) ph.dwc = ph.dwb;
-        else msm_sort_digits(ctx, wsl, nullptr, wn, 0, "wc", ph.dwc, wcfg, skip_c_);
+        else msm_sort_digits(ctx, wsl, widx, wn, 0, "wc", ph.dwc, wcfg, skip_c_);
     }
     ph.dA = skip_a_ ? &ph.dwa : &ph.dw;
     ph.dB = skip_b_ ? &ph.dwb : &ph.dw;

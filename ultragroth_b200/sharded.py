@@ -202,16 +202,24 @@ def _allgather_bytes(blob: bytes):
     if not dist.is_initialized() or dist.get_world_size() == 1:
         return [blob]
     mine = torch.frombuffer(bytearray(blob), dtype=torch.uint8)
+    world = dist.get_world_size()
     if dist.get_backend() == "nccl":
+        # one flat output and ONE device -> host read (a list of `world` tensors costs `world` small copies per exchange)
         mine = mine.cuda()
-    parts = [torch.empty_like(mine) for _ in range(dist.get_world_size())]
+        flat = torch.empty(world * mine.numel(), dtype=torch.uint8, device=mine.device)
+        dist.all_gather_into_tensor(flat, mine)
+        raw = flat.cpu().numpy().tobytes()
+        n = len(blob)
+        return [raw[i * n:(i + 1) * n] for i in range(world)]
+    parts = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(parts, mine)
-    return [bytes(p.cpu().numpy().tobytes()) for p in parts]
+    return [bytes(p.numpy().tobytes()) for p in parts]
 
 
 class ShardedProver:
-    """Point-range sharded Groth16 / UltraGroth prover: this process holds slice `rank` of `world` of every base array
-    (ugb_prover_create_sharded, include/ultragroth_b200.h).  `exchange` maps this rank's blob to the list of all ranks'
+    """Point-sharded Groth16 / UltraGroth prover: this process holds share `rank` of `world` of every base array
+    (ugb_prover_create_sharded, include/ultragroth_b200.h: H and the round bases by contiguous range, the witness-paired bases
+    interleaved, signal s on shard s % world).  `exchange` maps this rank's blob to the list of all ranks'
     blobs; the default is one torch.distributed all-gather.  The proof is assembled on `root` (None elsewhere)."""
 
     ERR = 512
@@ -335,29 +343,53 @@ class ShardedProver:
         self._phase("ugb_shard_finish", out)
         return out.raw
 
-    def prove2(self, wtns, rk=None, comm=None):
+    def prove2(self, wtns, rk=None, comm=None, trace=None):
         """Collective, phase by phase: this rank uploads only its witness slice, the slices are all-gathered between the GPUs, the three
         H-pipeline transforms run on up to three ranks and each rank receives its point range of a', b', c' (see DistComm).  Every rank
-        passes the same witness file (only rank `root` reads the public signals from it) and, for UltraGroth, the same r_k."""
+        passes the same witness file (only rank `root` reads the public signals from it) and, for UltraGroth, the same r_k.
+        trace: a dict that receives this rank's wall-clock milliseconds per phase; the stream is drained at every seam to attribute them,
+        so a traced proof is slower than an untraced one and its phases do not overlap (a diagnosis aid, never a bench number)."""
+        import time
         comm = comm or DistComm(self)
+        t_last = [time.perf_counter()]
+
+        def seam(name):
+            if trace is None:
+                return
+            comm.stream.synchronize()
+            now = time.perf_counter()
+            trace[name] = trace.get(name, 0.0) + (now - t_last[0]) * 1e3
+            t_last[0] = now
+
         with comm.stream_scope():
             self.upload_slice(wtns)
+            seam("upload_slice")
             comm.all_gather_witness()
+            seam("all_gather_witness")
             if self.ultra:
                 if rk is None:
                     raise ValueError("sharded UltraGroth proving needs a common r_k (draw it once and broadcast it)")
                 rounds = self.exchange(self.round_partial_resident())
+                seam("round_msm_and_exchange")
                 self.lookup(rounds, rk)
+                seam("lookup")
             self.h_transform(vector_mask(self.rank, self.world))
+            seam("h_transform")
             pending = comm.scatter_vectors()
             self.witness_msms()
+            seam("witness_msms")
             comm.wait(pending)
+            seam("scatter_wait")
             self.h_msm()
             mine = self.finish()
+            seam("h_msm_and_finish")
         parts = self.exchange(mine)
+        seam("exchange_partials")
         if self.root is not None and self.rank != self.root:
             return None
-        return self.assemble(parts, wtns=wtns, rk=rk)
+        out = self.assemble(parts, wtns=wtns, rk=rk)
+        seam("assemble")
+        return out
 
     def prove(self, wtns, rk=None):
         """Collective: every rank calls it with the same witness (and, for UltraGroth, the same r_k < 2^248)."""
