@@ -72,6 +72,17 @@ int ugb_msm_g1_xyzz(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, co
                     int window_bits, void* h_out_xyzz);
 int ugb_msm_g2_xyzz(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const uint32_t* d_index, uint64_t n,
                     int window_bits, void* h_out_xyzz);
+/* ugb_msm_g1 for callers that may not allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs and result as ugb_msm_g1 with d_index = NULL (bit-identical affine bytes), for n <= UGB_MSM_NOALLOC_MAX_POINTS; a larger
+ * n is refused (UGB_ERROR, ugb_last_error names the limit).  It calls no cudaMalloc / cudaFree / cudaMallocHost: all of its scratch
+ * is one fixed __device__ array of UGB_MSM_NOALLOC_SCRATCH_BYTES inside the library, which every GPU that runs this entry point holds
+ * until the process exits.  The array is shared by ALL calls on a device: calls that overlap on the GPU (two contexts, two host
+ * threads) race on it -- serialise them.  The call returns after its own stream has drained, like ugb_msm_g1. */
+#define UGB_MSM_NOALLOC_MAX_POINTS 16384u
+#define UGB_MSM_NOALLOC_SCRATCH_BYTES (8u * 1024u * 1024u + 4224u)
+int ugb_msm_g1_noalloc(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, uint64_t n, void* h_out);
+uint64_t ugb_msm_noalloc_max_points(void);
 /* host-side reduction of `count` XYZZ partial sums (from several GPUs / ranks) to one affine point */
 int ugb_g1_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out_affine);
 int ugb_g2_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out_affine);

@@ -129,6 +129,16 @@ int ugb_msm_g2(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, const u
     memcpy(h_out, &a, sizeof(a));
     return UGB_OK;
 }
+int ugb_msm_g1_noalloc(ugb_ctx* ctx, const void* d_bases, const void* d_scalars, uint64_t n, void* h_out) {
+    UGB_TRY
+    if (!ctx) throw std::invalid_argument("null ctx");
+    HG1XYZZ r;
+    msm_g1_noalloc(ctx->dev, d_bases, d_scalars, n, &r);
+    HG1Affine a = pt_to_affine(r);
+    memcpy(h_out, &a, sizeof(a));
+    UGB_CATCH
+}
+uint64_t ugb_msm_noalloc_max_points(void) { return MSM_NOALLOC_MAX_POINTS; }
 int ugb_g1_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out) {
     UGB_TRY
     HG1XYZZ acc = HG1XYZZ::inf();

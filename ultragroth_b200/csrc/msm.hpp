@@ -88,4 +88,10 @@ void msm_g1_launch_batch(DeviceCtx& ctx, const void* const* d_bases, int count, 
 void msm_g2_launch(DeviceCtx& ctx, const void* d_bases, const MsmDigits& dg, const std::string& slot);
 void msm_g2_finish(DeviceCtx& ctx, const MsmDigits& dg, const std::string& slot, HG2XYZZ* out);
 
+// G1 MSM that allocates nothing (msm_noalloc.cu): all scratch in one file-scope __device__ array of MSM_NOALLOC_SCRATCH_BYTES, so at
+// most MSM_NOALLOC_MAX_POINTS points; result XYZZ (128 B) to host memory.  Calls that overlap on one GPU race on the shared scratch.
+constexpr uint64_t MSM_NOALLOC_MAX_POINTS = 16384;
+constexpr uint64_t MSM_NOALLOC_SCRATCH_BYTES = 32ull * (MSM_NOALLOC_MAX_POINTS / 2048) * 256 * 128 + 33 * 128;  // 8 MiB + 4224 B
+void msm_g1_noalloc(DeviceCtx& ctx, const void* d_bases, const void* d_scalars, uint64_t n, void* h_out_xyzz);
+
 }  // namespace ug

@@ -94,6 +94,13 @@ class Context:
                  n, window_bits, out))
         return out.raw
 
+    def msm_g1_noalloc(self, bases: DeviceArray, scalars: DeviceArray, n) -> bytes:
+        """ugb_msm_g1_noalloc: the G1 MSM with all of its scratch in a fixed __device__ array (no device allocation on the call);
+        n <= lib().ugb_msm_noalloc_max_points().  Not in the reference."""
+        out = ctypes.create_string_buffer(64)
+        check(lib().ugb_msm_g1_noalloc(self.handle, bases.ptr, scalars.ptr, n, out))
+        return out.raw
+
     def ntt(self, data: DeviceArray, logn, inverse=False):
         """FFT<Fr>::fft / ifft: natural order in and out, in place."""
         check(lib().ugb_ntt(self.handle, data.ptr, logn, 1 if inverse else 0))
