@@ -357,7 +357,7 @@ def main():
             line["g1_msm"] = {
                 "h_points_per_s": world * n / ((stage["msm_h"] + stage["sort_h"]) * 1e-3), "h_points": n, "h_ms": stage["msm_h"] + stage["sort_h"],
                 "a_points_per_s": world * nvars / (stage["msm_a"] * 1e-3), "a_points": nvars, "a_ms": stage["msm_a"],
-                "note": "per-proof MSMs over resident window tables (c=22); standalone ad-hoc-base sweep: profiles/r01_sweep_g1.jsonl"}
+                "note": "per-proof MSMs over resident window tables (window picked by msm_pick_config: c=20 at 2^22); standalone ad-hoc-base sweep: profiles/r01_sweep_g1.jsonl"}
         line["prove_latency_ms"] = {"resident": 1000.0 * t_dev / args.steps, "e2e_single_call": 1000.0 * t_e2e_seq / args.steps,
                                     "e2e_pipelined_per_proof": 1000.0 * t_e2e / args.steps}
         line["roofline"], line["roofline_ntt"] = rooflines(stats, args, nvars, n, hbm_peak, peak_src, imad_wide, ultra, chunks, lookup_bits)

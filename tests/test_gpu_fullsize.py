@@ -11,7 +11,8 @@ With the blinding scalars r, s (and r_k) fixed, every quantity below is a canoni
     * the witness after compute_lookup filled it in                                             src/ultra_groth.cpp:62-106
     * the final proof points (the C API's JSON against the oracle's points)                     src/groth16.cpp:158-250
 The proofs go through the reference-facing C API (*_prover_prove, include/prover.h) on the resident-table MSM path the benchmark
-times (c = 22, one shared bucket set, multi-block reduction tails); the small-n tests force the same branches with UGB_MSM_PRE_C.
+times (c = 20 at these sizes, one shared bucket set, multi-block reduction tails); the small-n tests force the largest window, c = 22, with
+UGB_MSM_PRE_C.
 """
 import hashlib
 import json

@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--logn", type=int, default=22)
     ap.add_argument("--workload", default="ultragroth")
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--kernels", action="store_true", help="per-kernel device time of shard 0's witness_msms phase (profile mode: CUDA events per launch)")
     args = ap.parse_args()
     import torch
     import ultragroth_b200 as ug
@@ -55,6 +56,29 @@ def main():
             out[name] = sorted(ts)[len(ts) // 2]
         sp.finish()
         print("shard %d/%d: " % (r, args.world) + ", ".join("%s %.2f ms" % kv for kv in out.items()), flush=True)
+    if args.kernels:
+        import ctypes
+        from ultragroth_b200._lib import lib
+        L = lib()
+        sp = shards[0]
+        sp.witness_msms()
+        sp.finish()
+        L.ugb_prover_set_profile(sp.handle, 1)
+        reps = 3
+        for _ in range(reps):
+            sp.witness_msms()
+            sp.finish()
+        n = L.ugb_prover_kernel_stats(sp.handle, None, 0)
+        buf = ctypes.create_string_buffer(int(n) + 16)
+        L.ugb_prover_kernel_stats(sp.handle, buf, len(buf))
+        L.ugb_prover_set_profile(sp.handle, 0)
+        rows = []
+        for line in buf.value.decode().splitlines():
+            name, cnt, ms = line.split("\t")
+            rows.append((float(ms) / reps, int(cnt) // reps, name))
+        print("shard 0 witness_msms by kernel (ms per phase, launches): total %.2f ms" % sum(r[0] for r in rows))
+        for ms, cnt, name in sorted(rows, reverse=True):
+            print("  %-28s %3d  %.3f" % (name, cnt, ms))
     for sp in shards:
         sp.close()
 

@@ -22,15 +22,23 @@ MsmConfig msm_pick_config(uint64_t n, int force_c, bool pre) {
     if (force_c > 0) {
         best_c = std::min(std::max(force_c, 2), 23);
     } else {
-        // cost in modular multiplications: n*W mixed additions (10 each) + 2 additions (14 each) per bucket for the
-        // running-sum reduction + bucket memset / histogram traffic (~2 per bucket)
+        // cost in modular multiplications: n*W mixed additions (10 each) + the bucket reduction.
+        //   ad-hoc bases: W bucket sets, 2 additions (14 each) per bucket for the running sums + memset / histogram traffic (~2);
+        //   resident tables: ONE bucket set, but its reduction tails (chunked running sums, bit sums, segmented merge) are latency-
+        //   bound launches: calibrated on the witness-MSM phase of whole and of 1/2, 1/4, 1/8 sharded 2^22 provers they cost ~54
+        //   products per bucket next to the accumulation of witness-like scalars (profiles/r02_window_calibration.txt; the old 30
+        //   chose c = 22 where c = 20 proves 4 % faster).  A window that needs as many windows W as a smaller one only adds buckets
+        //   (c = 18 against 17, 21 against 20: measured slower every time), so only the smallest c of each W is a candidate.
+        const double per_bucket = pre ? 54.0 : 30.0;
         double best = 1e300;
         for (int c = 4; c <= (pre ? 22 : 20); c++) {
-            double W = (255 + c - 1) / c;
+            const int Wi = (255 + c - 1) / c;
+            if (pre && c > 4 && (255 + c - 2) / (c - 1) == Wi) continue;
+            double W = Wi;
             double B = (double)(1u << (c - 1));
             double sets = pre ? 1.0 : W;
             if ((double)n * W >= 2147483648.0) continue;  // table index + sign bit must fit 32 bits
-            double cost = (double)n * W * 10.0 + sets * B * 30.0;
+            double cost = (double)n * W * 10.0 + sets * B * per_bucket;
             if (cost < best) { best = cost; best_c = c; }
         }
         if (best_c == 0) best_c = 16;
@@ -50,6 +58,13 @@ MsmReducePlan msm_reduce_plan(const MsmConfig& cfg) {
     uint64_t total = (uint64_t)cfg.B * cfg.nwin();
     int mu = 2;
     while (mu < 8 && (total >> mu) > 65536) mu++;
+    if (cfg.pre) {
+        // one bucket set: a chunk of 2^mu buckets is a serial chain of 2 * 2^mu additions, the bit sums cost K * log2(K) / 2 additions
+        // over K = B / 2^mu chunk sums; measured optimum (tools/r02_rs_mu.sh): mu = 2..3 at B = 2^16, 4 at 2^18, 5..6 at 2^21
+        int lb = 0;
+        while ((1ull << (lb + 1)) <= cfg.B) lb++;
+        mu = std::min(8, std::max(2, (lb - 10) / 2));
+    }
     const int forced = env_int_msm("UGB_RS_MU", 0);  // experiment knob: chunk = 2^mu buckets
     if (forced >= 1 && forced <= 10) mu = forced;
     p.mu = mu;

@@ -39,7 +39,7 @@ MsmReducePlan msm_reduce_plan(const MsmConfig& cfg);
 
 // Resident bases with their window multiples: table[w*n + i] = 2^(c*w) * base[i], affine, zkey layout.
 // Costs W times the memory of the base array (HBM is 180 GB) and removes W-1 of the W bucket reductions; with the
-// reduction this cheap the window grows from c = 16 to c = 22 at n = 2^22, i.e. 12 instead of 16 additions per point.
+// reduction this cheap the window grows from c = 16 to c = 20 at n = 2^22 (22 at 2^24), i.e. 13 instead of 16 additions per point.
 struct MsmTable {
     void* d_table = nullptr;  // cudaMalloc'ed, owned by the caller (ProverDevice)
     uint64_t n = 0;
