@@ -230,6 +230,12 @@ int ugb_ultra_prove_assemble(void* prover_object, const void* partials, uint32_t
                              unsigned long long* proof_size, char* public_buffer, unsigned long long* public_size, char* error_msg,
                              unsigned long long error_msg_maxsize);
 
+/* The MSM planner's choice for n points (host arithmetic only, no device needed): window bits c, windows per scalar W = ceil(255 / c)
+ * and the running-sum chunk 2^chunk_log2 buckets.  resident_table != 0: bases with their 2^(c k) multiples resident (one shared
+ * bucket set, what a prover object uses); 0: ad-hoc bases (ugb_msm_*: one bucket set per window).  Honours UGB_MSM_PRE_C / UGB_MSM_C /
+ * UGB_RS_MU like the MSMs themselves.  For tests and for sizing HBM (tables take W times the base array). */
+int ugb_msm_plan(uint64_t n, int resident_table, int* c, int* windows, int* chunk_log2);
+
 /* ---- microbenchmarks for the roofline denominators ----
  * kind 0: independent 32-bit IMAD chains; 1: IMAD.WIDE (mad.wide.u32) chains; 2: dependent Fq Montgomery
  * products (4 chains per thread); 3 / 4: IMAD.WIDE rows with carry-in+out / carry-out only; 5: kind 2 on the Karatsuba product

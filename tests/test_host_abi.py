@@ -87,3 +87,40 @@ def test_no_gpu_means_loud_failure_not_a_cpu_fallback():
     with pytest.raises(up.ProverError) as ei:
         up.Prover(zk)
     assert ei.value.code == up.PROVER_ERROR and "no CPU fallback" in ei.value.msg
+
+
+def _plan(n, resident):
+    c, w, mu = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    assert ug.lib().ugb_msm_plan(ctypes.c_uint64(n), 1 if resident else 0, ctypes.byref(c), ctypes.byref(w), ctypes.byref(mu)) == 0
+    return c.value, w.value, mu.value
+
+
+def test_msm_window_planner(monkeypatch):
+    """The planner is host arithmetic (csrc/msm.cu: msm_pick_config, msm_reduce_plan), calibrated on measured reduction-tail costs
+    (profiles/r02_window_calibration.txt): the windows it must choose at the sizes that were measured, and its invariants."""
+    for k in ("UGB_MSM_PRE_C", "UGB_MSM_C", "UGB_RS_MU"):
+        monkeypatch.delenv(k, raising=False)
+    # resident tables: whole 2^22 UltraGroth prover (witness arrays 5.3 M, H 4.19 M), its 1/2 and 1/8 shards, 2^24 Groth16
+    assert _plan(5308415, True)[:2] == (20, 13)
+    assert _plan(1 << 22, True)[:2] == (20, 13)
+    assert _plan(5308415 // 2, True)[:2] == (20, 13)
+    assert _plan(663552, True)[:2] == (17, 15)
+    assert _plan(1 << 19, True)[:2] == (17, 15)
+    assert _plan((1 << 24) + 3, True)[:2] == (22, 12)
+    prev = 0
+    for logn in range(8, 27):
+        c, w, mu = _plan(1 << logn, True)
+        assert w == -(-255 // c) and 4 <= c <= 22
+        assert c == 4 or -(-255 // (c - 1)) != w, "only the smallest window of each W is a candidate"
+        assert c >= prev, "the window never shrinks as n grows"
+        lb = c - 1
+        assert mu == min(8, max(2, (lb - 10) // 2))
+        prev = c
+    # ad-hoc bases (one bucket set per window): unchanged rule, c <= 20, chunks sized for ~64 Ki threads over all windows
+    for logn in (10, 16, 20, 24, 26):
+        c, w, mu = _plan(1 << logn, False)
+        assert 4 <= c <= 20 and w == -(-255 // c) and 2 <= mu <= 8
+    # the experiment knobs are honoured
+    monkeypatch.setenv("UGB_MSM_PRE_C", "22")
+    monkeypatch.setenv("UGB_RS_MU", "6")
+    assert _plan(1000, True) == (22, 12, 6)

@@ -49,6 +49,7 @@ def _declare(L):
     for name in ("ugb_msm_g1", "ugb_msm_g2", "ugb_msm_g1_xyzz", "ugb_msm_g2_xyzz"):
         getattr(L, name).argtypes = [vp, vp, vp, vp, u64, i32, vp]
     L.ugb_msm_g1_noalloc.argtypes = [vp, vp, vp, u64, vp]
+    L.ugb_msm_plan.argtypes = [u64, i32, c.POINTER(i32), c.POINTER(i32), c.POINTER(i32)]
     L.ugb_msm_noalloc_max_points.restype = u64
     L.ugb_msm_noalloc_max_points.argtypes = []
     L.ugb_g1_sum_xyzz_to_affine.argtypes = [vp, u64, vp]

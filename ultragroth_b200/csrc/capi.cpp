@@ -139,6 +139,15 @@ int ugb_msm_g1_noalloc(ugb_ctx* ctx, const void* d_bases, const void* d_scalars,
     UGB_CATCH
 }
 uint64_t ugb_msm_noalloc_max_points(void) { return MSM_NOALLOC_MAX_POINTS; }
+int ugb_msm_plan(uint64_t n, int resident_table, int* c, int* windows, int* chunk_log2) {
+    UGB_TRY
+    const MsmConfig cfg = msm_pick_config(n, 0, resident_table != 0);
+    const MsmReducePlan plan = msm_reduce_plan(cfg);
+    if (c) *c = cfg.c;
+    if (windows) *windows = cfg.W;
+    if (chunk_log2) *chunk_log2 = plan.mu;
+    UGB_CATCH
+}
 int ugb_g1_sum_xyzz_to_affine(const void* h_partials, uint64_t count, void* h_out) {
     UGB_TRY
     HG1XYZZ acc = HG1XYZZ::inf();
