@@ -207,8 +207,9 @@ int ugb_proof_points_to_json(int ultra, const void* A64, const void* B128, const
 
 /* ---- point-range sharded proving ("MSMs shard by point range across GPUs, partial sums reduced
  * on the host or via NCCL") ----
- * One prover object per GPU / process keeps slice `rank` of `world` of every zkey base array resident (A, B1, B2, C,
- * H, UltraGroth's round C); witness, coefficients and the H pipeline are replicated.  The MSM partial sums are opaque
+ * One prover object per GPU / process keeps share `rank` of `world` of every zkey base array resident (H and UltraGroth's
+ * round C: a contiguous range; A, B1, B2, C: the points of signals rank, rank + world, ... -- see ugb_shard_layout); witness,
+ * coefficients and the H pipeline are replicated on this first protocol (the phase-wise ugb_shard_* protocol below shards them too).  The MSM partial sums are opaque
  * host blobs of ugb_prover_partial_size() bytes; the caller exchanges them (one all-gather) and any rank assembles.
  * They replace, per shard, the MSM calls of src/groth16.cpp:53-64,153-154 / src/ultra_groth.cpp:168,203-234,329; the
  * assemble calls are src/groth16.cpp:158-250 / src/ultra_groth.cpp:337-399,476-513.  Return codes as include/prover.h. */

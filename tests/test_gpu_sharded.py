@@ -1,4 +1,5 @@
-"""GPU: point-range sharded proving.  Every shard holds 1/world of each base array and returns
+"""GPU: sharded proving.  Every shard holds 1/world of each base array (H and the round bases by contiguous range, the
+witness-paired bases interleaved: signal s on shard s % world -- world 3 and 5 make the shares ragged) and returns
 partial MSM sums; the assembled proof must be BYTE-IDENTICAL to the unsharded prover's for the same blinding, at every
 world size (the shard sums are a re-association of the same group sum, and the proof is an affine, canonical value).
 

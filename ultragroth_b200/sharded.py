@@ -2,6 +2,9 @@
 [lo, hi) of a base array resident and receives only its slice of the scalars; the exchange is one all-gather
 of the XYZZ partial sums (128 B per rank for G1, 256 B for G2) followed by world-1 point additions on the
 host (ugb_g1_sum_xyzz_to_affine).  torch.distributed is plumbing only (NCCL on GPUs, gloo in the CPU tests).
+That is the standalone MSM (ShardedMsm, sweep.py).  Inside a ShardedProver only H, the round bases and the witness UPLOAD are cut
+into such contiguous ranges; the witness-paired bases (A, B1, B2, C) are dealt out interleaved, signal s on shard s % world, so that
+every shard sees the same mix of small and full-width scalars.
 """
 import ctypes
 
