@@ -137,8 +137,11 @@ def test_two_process_gloo(tmp_path):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
     env = dict(os.environ, UGB_ROOT=ROOT, MASTER_ADDR="127.0.0.1")
-    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-                          "--master-port", str(_free_port()), str(script)], env=env, capture_output=True, text=True, timeout=600)
+    for attempt in range(2):  # the free port is released before torchrun binds it: one more attempt on a fresh port if the launch fails
+        out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                              "--master-port", str(_free_port()), str(script)], env=env, capture_output=True, text=True, timeout=600)
+        if out.returncode == 0:
+            break
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     # the two ranks share one pipe: their "ok <rank>" lines may interleave character by character
     assert out.stdout.count("ok") == 2 and "0" in out.stdout and "1" in out.stdout

@@ -345,6 +345,7 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
     UG_CUDA_CHECK(cudaStreamCreateWithFlags(&up, cudaStreamNonBlocking));
     std::vector<cudaEvent_t> up_events;
     std::vector<void*> garbage;  // level-0 base arrays superseded by their tables, scratch copies
+    std::vector<std::vector<uint8_t>> staged;  // host gathers of a shard's interleaved points; declared before `cleanup` so that they outlive its stream sync
     struct Cleanup {
         cudaStream_t& up; std::vector<cudaEvent_t>& ev; std::vector<void*>& g; DeviceCtx& ctx;
         ~Cleanup() {
@@ -361,7 +362,6 @@ void ProverDevice::construct(const ZkeyData& zk, uint32_t shard_rank, uint32_t s
     };
     // this shard's points of a witness-paired array: the whole array when unsharded, else points rank, rank + world, ... gathered on
     // the host (threads over ranges of j) into a buffer that lives until the end of construct
-    std::vector<std::vector<uint8_t>> staged;
     auto upload_own = [&](const uint8_t* src, size_t elem) -> void* {
         if (shard_world == 1) return upload_up(src, (size_t)wn * elem);
         staged.emplace_back((size_t)wn * elem);
