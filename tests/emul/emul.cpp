@@ -3,6 +3,7 @@
 // formulas on the GPU-less build box.  Never loaded by the ultragroth_b200 package; the product
 // library runs these algorithms on the device only.
 #include "../../ultragroth_b200/csrc/curve.cuh"
+#include "../../ultragroth_b200/csrc/msm.cuh"
 #include <cstring>
 using namespace ug;
 
@@ -47,5 +48,21 @@ int emul_field_op(int field, int op, const uint32_t* a, const uint32_t* b, uint3
 int emul_point_op(int group, int op, const void* acc, const void* q, int neg, void* out) {
     if (group == 1) point_op<Fq>(op, acc, q, neg, out); else point_op<Fq2>(op, acc, q, neg, out);
     return 0;
+}
+
+// next_bucket (msm.cuh): the accumulation kernels' step to the next non-empty bucket.  starts: NB + 1 offsets.
+uint32_t emul_next_bucket(const uint32_t* starts, uint32_t NB, uint32_t key, uint32_t pos, uint32_t* end_out) {
+    uint32_t end = 0;
+    next_bucket(starts, NB, key, pos, end);
+    *end_out = end;
+    return key;
+}
+// signed-digit recoding of one scalar (msm.cuh: scalar_reduce + scalar_digits): out[w] = signed digit of window w
+void emul_scalar_digits(const uint32_t* scalar8, int c, int W, int32_t* out) {
+    Scalar256 s;
+    memcpy(s.v, scalar8, 32);
+    scalar_reduce(s);
+    for (int w = 0; w < W; w++) out[w] = 0;
+    scalar_digits(s, c, W, [&](int w, uint32_t b, bool neg) { out[w] = neg ? -(int32_t)(b + 1) : (int32_t)(b + 1); });
 }
 }

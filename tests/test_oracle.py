@@ -49,12 +49,15 @@ def emul():
     os.makedirs(out, exist_ok=True)
     lib = os.path.join(out, "libemul.so")
     src = os.path.join(HERE, "emul", "emul.cpp")
-    deps = [src] + [os.path.join(HERE, "..", "ultragroth_b200", "csrc", f) for f in ("ff.cuh", "curve.cuh")]
+    deps = [src] + [os.path.join(HERE, "..", "ultragroth_b200", "csrc", f) for f in ("ff.cuh", "curve.cuh", "memops.cuh", "msm.cuh")]
     if not os.path.exists(lib) or any(os.path.getmtime(lib) < os.path.getmtime(d) for d in deps):
         subprocess.check_call(["g++", "-O1", "-std=c++17", "-fPIC", "-shared", "-o", lib, src])
     L = ctypes.CDLL(lib)
     L.emul_field_op.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long]
     L.emul_point_op.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    L.emul_next_bucket.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]
+    L.emul_next_bucket.restype = ctypes.c_uint32
+    L.emul_scalar_digits.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
     return L
 
 
@@ -447,3 +450,49 @@ int main() {
     subprocess.check_call(["g++", "-O2", "-std=c++17", "-I", os.path.join(root, "ultragroth_b200", "csrc"), str(src), "-o", str(exe)])
     out = subprocess.run([str(exe)], capture_output=True, text=True)
     assert out.returncode == 0 and "mismatches 0" in out.stdout, out.stdout + out.stderr
+
+
+def test_next_bucket_equals_the_linear_walk(emul):
+    """msm.cuh next_bucket (two probes, then a binary search) against the plain walk it replaced, on bucket offset arrays with long
+    runs of EMPTY buckets -- the case that stalled a thread of shard 0 for 2*10^5 steps."""
+    import numpy as np
+    rng = np.random.default_rng(7)
+    for trial in range(40):
+        NB = int(rng.integers(3, 5000))
+        counts = np.zeros(NB, dtype=np.uint32)
+        live = rng.random(NB) < rng.choice([0.001, 0.02, 0.3, 0.9])
+        live[int(rng.integers(0, NB))] = True
+        counts[live] = rng.integers(1, 9, size=int(live.sum()))
+        starts = np.zeros(NB + 1, dtype=np.uint32)
+        starts[1:] = np.cumsum(counts)
+        M = int(starts[NB])
+        end_out = ctypes.c_uint32()
+        for _ in range(60):
+            pos = int(rng.integers(0, M))
+            # any bucket that does not reach beyond pos is a legal starting point (the kernel starts from the bucket that ENDS at pos)
+            owner = int(np.searchsorted(starts[1:], pos, side="right"))
+            key = int(rng.integers(-1, owner)) if owner > 0 else -1
+            want = key + 1
+            while starts[want + 1] <= pos:
+                want += 1
+            got = emul.emul_next_bucket(starts.ctypes.data, NB, key & 0xFFFFFFFF, pos, ctypes.byref(end_out))
+            assert got == want == owner and end_out.value == int(starts[want + 1]), (trial, NB, key, pos)
+
+
+def test_signed_digit_recoding_reconstructs_the_scalar(emul):
+    """msm.cuh scalar_reduce + scalar_digits: W = ceil(255 / c) signed digits with |d| <= 2^(c-1) whose weighted sum is the scalar mod r,
+    for every window size the planner can pick (and the forced ones), on boundary scalars and random 256-bit values."""
+    import numpy as np
+    rng = random.Random(11)
+    specials = [0, 1, 2, bn.R - 1, bn.R, bn.R + 1, (1 << 256) - 1, (1 << 255), (1 << 254) - 1, (1 << 253), (1 << 128) - 1]
+    for c in (4, 8, 13, 15, 16, 17, 19, 20, 22, 23):
+        W = -(-255 // c)
+        half = 1 << (c - 1)
+        specials_c = specials + [half, half + 1, half - 1, (half << c) | half, sum(half << (c * w) for w in range(W)) % (1 << 256),
+                                 sum((half + 1) << (c * w) for w in range(W - 1))]
+        for s in specials_c + [rng.getrandbits(256) for _ in range(200)]:
+            out = (ctypes.c_int32 * W)()
+            emul.emul_scalar_digits(int(s).to_bytes(32, "little"), c, W, out)
+            digits = list(out)
+            assert all(-(half - 1) <= d <= half for d in digits), (c, hex(s), digits)
+            assert sum(d << (c * w) for w, d in enumerate(digits)) == s % bn.R, (c, hex(s))

@@ -68,6 +68,25 @@ UG_HD void scalar_digits(const Scalar256& s, int c, int W, Fn f) {
     }
 }
 
+// The next non-empty bucket after `key`: the smallest k > key with starts[k + 1] > pos.  Dense digit distributions find it at the
+// first or second probe; a shard that holds only small scalars leaves ~2^21 empty buckets between two windows, and a linear walk
+// over them stalls one thread (and with it its whole launch: 5 ms kernels at 2 % pipe use on shard 0 of 8) -- so after two probes
+// the search is binary.  Caller guarantees pos < starts[NB].  (Host-callable so that tests/emul can check it without a GPU.)
+UG_HD void next_bucket(const uint32_t* starts, uint32_t NB, uint32_t& key, uint32_t pos, uint32_t& end) {
+    key++; end = starts[key + 1];
+    if (end > pos) return;
+    key++; end = starts[key + 1];
+    if (end > pos) return;
+    uint32_t a = key + 1, b = NB - 1;
+    while (a < b) {
+        uint32_t mid = (a + b) >> 1;
+        if (starts[mid + 1] > pos) b = mid; else a = mid + 1;
+    }
+    key = a; end = starts[key + 1];
+}
+
+#if defined(__CUDACC__)
+
 UG_D Scalar256 load_scalar(const uint8_t* scalars, const uint32_t* index, uint64_t i) {
     uint64_t src = index ? (uint64_t)index[i] : i;
     const uint4* p = reinterpret_cast<const uint4*>(scalars + src * 32);
@@ -77,8 +96,6 @@ UG_D Scalar256 load_scalar(const uint8_t* scalars, const uint32_t* index, uint64
     s.v[4] = b.x; s.v[5] = b.y; s.v[6] = b.z; s.v[7] = b.w;
     return s;
 }
-
-#if defined(__CUDACC__)
 
 // key_stride / entry_stride select the bucket layout:
 //   per-window bucket sets (ad-hoc bases):   key = w*B + |d|-1,  entry = i                 (key_stride = B, entry_stride = 0)
@@ -226,23 +243,6 @@ __global__ void __launch_bounds__(SCAN_BS) k_scan_apply(const uint32_t* __restri
 // [t*L, (t+1)*L), L = ceil(M/T).  Outputs: buckets[key] for runs strictly inside the slice,
 // (pkeys, ppts)[2t], [2t+1] for the first and last run of the slice.  key_off / key_none: several MSMs that share one digit sort
 // are reduced together (msm.cu: batch): pkeys carry key + key_off (position in the concatenated bucket array), key_none = "no run".
-// The next non-empty bucket after `key`: the smallest k > key with starts[k + 1] > pos.  Dense digit distributions find it at the
-// first or second probe; a shard that holds only small scalars leaves ~2^21 empty buckets between two windows, and a linear walk
-// over them stalls one thread (and with it its whole launch: 5 ms kernels at 2 % pipe use on shard 0 of 8) -- so after two probes
-// the search is binary.  Caller guarantees pos < starts[NB].
-__device__ __forceinline__ void next_bucket(const uint32_t* __restrict__ starts, uint32_t NB, uint32_t& key, uint32_t pos, uint32_t& end) {
-    key++; end = starts[key + 1];
-    if (end > pos) return;
-    key++; end = starts[key + 1];
-    if (end > pos) return;
-    uint32_t a = key + 1, b = NB - 1;
-    while (a < b) {
-        uint32_t mid = (a + b) >> 1;
-        if (starts[mid + 1] > pos) b = mid; else a = mid + 1;
-    }
-    key = a; end = starts[key + 1];
-}
-
 template <class F>
 __global__ void __launch_bounds__(128, sizeof(F) == 32 ? 4 : 1) k_accumulate(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ entries,
                                                     const uint32_t* __restrict__ starts, uint32_t NB,
