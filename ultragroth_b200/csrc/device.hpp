@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <map>
 #include <stdexcept>
 #include <string>
@@ -55,6 +56,11 @@ public:
                                      std::to_string(prop.minor) + "; this library is built for sm_100a (B200) only");
         }
         UG_CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        // experiment knob: L2 fetch granularity in bytes (32 / 64 / 128; a device-wide hint).  The bucket accumulation gathers 64-byte
+        // points at random and ncu counts ~147 B of DRAM traffic per entry: is that the 128-byte L2 line fill?
+        if (const char* g = getenv("UGB_L2_FETCH")) {
+            if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(g)) != cudaSuccess) cudaGetLastError();
+        }
     }
     ~DeviceCtx() {
         cudaSetDevice(device);
