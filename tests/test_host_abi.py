@@ -124,3 +124,19 @@ def test_msm_window_planner(monkeypatch):
     monkeypatch.setenv("UGB_MSM_PRE_C", "22")
     monkeypatch.setenv("UGB_RS_MU", "6")
     assert _plan(1000, True) == (22, 12, 6)
+
+
+def test_noalloc_msm_limits_agree_between_header_and_library():
+    """ugb_msm_g1_noalloc's stated maximum (include/ultragroth_b200.h) is what the library enforces, its scratch footprint is the
+    one the header states, and without a context the call is refused before anything touches a device."""
+    text = open(os.path.join(ROOT, "include", "ultragroth_b200.h")).read()
+    max_points = int(re.search(r"#define UGB_MSM_NOALLOC_MAX_POINTS (\d+)u", text).group(1))
+    L = ug.lib()
+    assert int(L.ugb_msm_noalloc_max_points()) == max_points == 16384
+    m = re.search(r"#define UGB_MSM_NOALLOC_SCRATCH_BYTES \((\d+)u \* (\d+)u \* (\d+)u \+ (\d+)u\)", text)
+    a, b, c, d = (int(x) for x in m.groups())
+    # 32 windows x (max_points / 2048) slices x 256 buckets x 128 B, + 33 window / result points (csrc/msm_noalloc.cu)
+    assert a * b * c + d == 32 * (max_points // 2048) * 256 * 128 + 33 * 128
+    out = ctypes.create_string_buffer(64)
+    assert L.ugb_msm_g1_noalloc(None, None, None, 1, out) != 0
+    assert b"ctx" in L.ugb_last_error()
